@@ -1,0 +1,208 @@
+"""ctypes binding of the C ABI in include/bf_cuda.h (libbfcuda.so).
+
+This is the only way Python code in this repo reaches the product: tests, bench.py and
+__graft_entry__ all call the same `extern "C"` entry points a C host program would.  There is no
+fallback of any kind: if the shared library is missing, importing a symbol from it raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+PKG_DIR = Path(__file__).resolve().parent
+REPO_ROOT = PKG_DIR.parent
+LIB_DIR = PKG_DIR / "lib"
+LIB_PATH = LIB_DIR / "libbfcuda.so"
+ATTACH_LIB_PATH = LIB_DIR / "libbfcuda_attach.so"
+
+ABI_VERSION = 1
+
+# enums (include/bf_cuda.h)
+OK = 0
+REAL_F64, COMPLEX_F64 = 0, 1
+OP_N, OP_T, OP_H = 0, 1, 2
+LEAF_DENSE, LEAF_IDENTITY, LEAF_DIAG = 0, 1, 2
+LEAF_TRANS, LEAF_CONJ = 2, 4
+BUF_X, BUF_Y, BUF_FIRST_TEMP = 0, 1, 2
+
+
+class RawOp(C.Structure):
+    """struct BfCudaRawOp"""
+
+    _fields_ = [
+        ("kind", C.c_int32),
+        ("flags", C.c_uint32),
+        ("inBuf", C.c_int64),
+        ("inOff", C.c_int64),
+        ("outBuf", C.c_int64),
+        ("outOff", C.c_int64),
+        ("m", C.c_int64),
+        ("k", C.c_int64),
+        ("ld", C.c_int64),
+        ("val", C.c_void_p),
+    ]
+
+
+RAWOP_DTYPE = np.dtype(
+    [
+        ("kind", "<i4"),
+        ("flags", "<u4"),
+        ("inBuf", "<i8"),
+        ("inOff", "<i8"),
+        ("outBuf", "<i8"),
+        ("outOff", "<i8"),
+        ("m", "<i8"),
+        ("k", "<i8"),
+        ("ld", "<i8"),
+        ("val", "<u8"),
+    ],
+    align=True,
+)
+assert RAWOP_DTYPE.itemsize == C.sizeof(RawOp) == 72
+
+
+class PlanDesc(C.Structure):
+    """struct BfCudaPlanDesc"""
+
+    _fields_ = [
+        ("abiVersion", C.c_int32),
+        ("dtype", C.c_int32),
+        ("numRows", C.c_int64),
+        ("numCols", C.c_int64),
+        ("numBufs", C.c_int64),
+        ("bufRows", C.POINTER(C.c_int64)),
+        ("numOps", C.c_int64),
+        ("ops", C.POINTER(RawOp)),
+        ("device", C.c_int32),
+        ("buildTranspose", C.c_int32),
+    ]
+
+
+class PlanInfo(C.Structure):
+    """struct BfCudaPlanInfo"""
+
+    _fields_ = [
+        ("dtype", C.c_int32),
+        ("device", C.c_int32),
+        ("numRows", C.c_int64),
+        ("numCols", C.c_int64),
+        ("numOps", C.c_int64),
+        ("numEntries", C.c_int64),
+        ("numStagesN", C.c_int64),
+        ("numStagesT", C.c_int64),
+        ("numItemsN", C.c_int64),
+        ("numTilesN", C.c_int64),
+        ("poolBytes", C.c_int64),
+        ("tableBytes", C.c_int64),
+        ("workspaceRowsN", C.c_int64),
+        ("workspaceRowsT", C.c_int64),
+        ("maxTileK", C.c_int64),
+        ("maxItemRows", C.c_int64),
+    ]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# every symbol include/bf_cuda.h declares; tests check that the .so exports all of them
+EXPORTED_SYMBOLS = [
+    "bfCudaPlanCreate",
+    "bfCudaPlanDestroy",
+    "bfCudaPlanGetInfo",
+    "bfCudaPlanFillSynthetic",
+    "bfCudaSyntheticValue",
+    "bfCudaPlanGetOpPoolOffset",
+    "bfCudaPlanSetPerms",
+    "bfCudaApplyDevice",
+    "bfCudaApplyHost",
+    "bfCudaPlanLastLaunchCount",
+    "bfCudaPlanSetProfiling",
+    "bfCudaPlanGetStageTimes",
+    "bfCudaRawOpsSave",
+    "bfCudaRawOpsLoad",
+    "bfCudaRawOpsFree",
+    "bfCudaStatusString",
+    "bfCudaLastErrorMessage",
+    "bfCudaAbiVersion",
+]
+ATTACH_EXPORTED_SYMBOLS = [
+    "bfCudaFlatten",
+    "bfCudaFlattenFree",
+    "bfCudaMatAttach",
+    "bfCudaMatDetach",
+    "bfCudaMatGetPlan",
+    "bfCudaMatSetPerms",
+]
+
+_lib = None
+
+
+class BfCudaError(RuntimeError):
+    def __init__(self, status, where, detail=""):
+        self.status = status
+        super().__init__(f"{where}: status {status} ({detail})")
+
+
+def load_library(path: os.PathLike | None = None) -> C.CDLL:
+    """dlopen libbfcuda.so and declare prototypes.  Raises if the library is absent: the product
+    has no other path."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise FileNotFoundError(
+            f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback)"
+        )
+    lib = C.CDLL(str(p), mode=C.RTLD_GLOBAL)
+    vp, i32, i64, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64
+    lib.bfCudaPlanCreate.argtypes = [C.POINTER(PlanDesc), C.POINTER(vp)]
+    lib.bfCudaPlanCreate.restype = i32
+    lib.bfCudaPlanDestroy.argtypes = [vp]
+    lib.bfCudaPlanDestroy.restype = i32
+    lib.bfCudaPlanGetInfo.argtypes = [vp, C.POINTER(PlanInfo)]
+    lib.bfCudaPlanGetInfo.restype = i32
+    lib.bfCudaPlanFillSynthetic.argtypes = [vp, u64]
+    lib.bfCudaPlanFillSynthetic.restype = i32
+    lib.bfCudaSyntheticValue.argtypes = [u64, i64, i32, i64]
+    lib.bfCudaSyntheticValue.restype = C.c_double
+    lib.bfCudaPlanGetOpPoolOffset.argtypes = [vp, i64, C.POINTER(i64), C.POINTER(i64)]
+    lib.bfCudaPlanGetOpPoolOffset.restype = i32
+    lib.bfCudaPlanSetPerms.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    lib.bfCudaPlanSetPerms.restype = i32
+    lib.bfCudaApplyDevice.argtypes = [vp, i32, vp, i64, i64, vp, i64, vp]
+    lib.bfCudaApplyDevice.restype = i32
+    lib.bfCudaApplyHost.argtypes = [vp, i32, vp, i64, i64, vp, i64]
+    lib.bfCudaApplyHost.restype = i32
+    lib.bfCudaPlanLastLaunchCount.argtypes = [vp]
+    lib.bfCudaPlanLastLaunchCount.restype = i64
+    lib.bfCudaPlanSetProfiling.argtypes = [vp, i32]
+    lib.bfCudaPlanSetProfiling.restype = i32
+    lib.bfCudaPlanGetStageTimes.argtypes = [vp, C.POINTER(C.c_float), i64, C.POINTER(i64)]
+    lib.bfCudaPlanGetStageTimes.restype = i32
+    lib.bfCudaRawOpsSave.argtypes = [C.POINTER(PlanDesc), C.c_char_p]
+    lib.bfCudaRawOpsSave.restype = i32
+    lib.bfCudaRawOpsLoad.argtypes = [C.c_char_p, C.POINTER(C.POINTER(PlanDesc))]
+    lib.bfCudaRawOpsLoad.restype = i32
+    lib.bfCudaRawOpsFree.argtypes = [C.POINTER(PlanDesc)]
+    lib.bfCudaRawOpsFree.restype = None
+    lib.bfCudaStatusString.argtypes = [i32]
+    lib.bfCudaStatusString.restype = C.c_char_p
+    lib.bfCudaLastErrorMessage.argtypes = []
+    lib.bfCudaLastErrorMessage.restype = C.c_char_p
+    lib.bfCudaAbiVersion.argtypes = []
+    lib.bfCudaAbiVersion.restype = i32
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def check(status: int, where: str):
+    if status != OK:
+        lib = load_library()
+        detail = lib.bfCudaLastErrorMessage()
+        raise BfCudaError(status, where, (detail or b"").decode(errors="replace"))

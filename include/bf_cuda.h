@@ -1,0 +1,208 @@
+/* bf_cuda.h — C ABI of libbfcuda.so: the B200 (sm_100a) butterfly-apply engine.
+ *
+ * This is the drop-in boundary for ONE path of sampotter/butterfly: applying a
+ * precomputed butterfly factorization (a BfMat tree of MatProduct / MatBlockDiag /
+ * MatBlockCoo / MatBlockDense nodes with dense, identity and diagonal leaves) to a block of
+ * right-hand sides.  Everything here is `extern "C"`, plain pointers and sizes; there are no
+ * reference types and no torch types in any signature.  The reference-facing half (walking a
+ * `BfMat *` and swapping its vtable) is in bf_cuda_attach.h and is built on top of this file.
+ *
+ * Reference interfaces replaced (paths relative to the reference tree):
+ *   bfMatMul / bfMatMulVec / bfMatRmul / bfMatRmulVec      src/mat.c:183-201
+ *   bfMatProductMul / MulVec / Rmul / RmulVec              src/mat_product.c:211-345
+ *   bfMatBlockDiagMul / MulVec / RmulVec                   src/mat_block_diag.c:370-505
+ *   bfMatBlockCooMul / MulVec / RmulVec                    src/mat_block_coo.c:382-520
+ *   bfMatBlockDenseMul / MulVec / Rmul / RmulVec           src/mat_block_dense.c:512-758
+ *   bfMatDenseComplexMul (cblas_zgemm)                     src/mat_dense_complex.c:1024-1051,1704-1765
+ *   bfMatDenseRealMulVec / RmulVec (cblas_dgemv)           src/mat_dense_real.c:1340-1441
+ *   bfMatIdentityMul / MulVec / RmulVec                    src/mat_identity.c:149-199
+ *   bfMatDiagRealMulVec                                    src/mat_diag_real.c:168
+ *   bfMatDenseComplexPermuteRows / bfVecRealPermute        src/mat_dense_complex.c:741-774, src/vec_real.c:312-330
+ *
+ * Model.  The recursive operator is flattened ONCE into a list of "raw ops".  Each raw op is
+ * one leaf of the tree together with where its operand comes from and where its result is
+ * accumulated:
+ *
+ *        out[outBuf][outOff : outOff + m, :]  +=  op(block) * in[inBuf][inOff : inOff + k, :]
+ *
+ * Buffers are "virtual vectors" (row blocks of an n x nrhs matrix): buffer 0 is the operand X,
+ * buffer 1 is the result Y, buffers >= 2 are the intermediates a MatProduct creates between its
+ * factors (src/mat_product.c:225-238).  Every buffer starts at zero (bfMatZerosLike,
+ * src/mat_block_coo.c:401; rows of a MatBlockDiag result that no block covers are
+ * uninitialised in the reference, src/mat_block_diag.c:384 — we define them as zero).
+ * bfCudaPlanCreate compiles the raw ops into a device-resident, stage-major packed layout
+ *  and owns all device memory.
+ *
+ * Errors: every function returns a BfCudaStatus; nothing aborts.  The reference's convention
+ * (global error code + NULL, src/error.c:5-24) is reproduced by the attach layer.
+ *
+ * There is NO CPU fallback: if no CUDA device is usable, bfCudaPlanCreate fails with
+ * BF_CUDA_ERROR_NO_DEVICE.
+ */
+#ifndef BF_CUDA_H
+#define BF_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BF_CUDA_ABI_VERSION 1
+
+typedef enum BfCudaStatus {
+  BF_CUDA_OK = 0,
+  BF_CUDA_ERROR_INVALID_ARGUMENT = 1, /* ~ BF_ERROR_INVALID_ARGUMENTS (include/bf/error.h) */
+  BF_CUDA_ERROR_NOT_IMPLEMENTED = 2,  /* ~ BF_ERROR_NOT_IMPLEMENTED */
+  BF_CUDA_ERROR_OUT_OF_MEMORY = 3,    /* ~ BF_ERROR_MEMORY_ERROR */
+  BF_CUDA_ERROR_RUNTIME = 4,          /* ~ BF_ERROR_RUNTIME_ERROR (a CUDA call failed) */
+  BF_CUDA_ERROR_NO_DEVICE = 5,
+  BF_CUDA_ERROR_IO = 6,               /* ~ BF_ERROR_FILE_ERROR */
+  BF_CUDA_ERROR_INCOMPATIBLE_SHAPES = 7 /* ~ BF_ERROR_INCOMPATIBLE_SHAPES */
+} BfCudaStatus;
+
+typedef enum BfCudaDtype {
+  BF_CUDA_REAL_F64 = 0,   /* BfReal = double              (include/bf/def.h:23-34) */
+  BF_CUDA_COMPLEX_F64 = 1 /* BfComplex = double _Complex, interleaved (re, im) */
+} BfCudaDtype;
+
+/* Which operator is applied.  N: Y = A X (bfMatMul / bfMatMulVec).  T: Y = A^T X
+ * (bfMatRmulVec on the real path, src/mat_product.c:312-345).  H: Y = A^H X (what
+ * bfMatTranspose means for complex dense leaves: it sets TRANS and CONJ,
+ * src/mat_dense_complex.c:1475-1478). */
+typedef enum BfCudaOp { BF_CUDA_OP_N = 0, BF_CUDA_OP_T = 1, BF_CUDA_OP_H = 2 } BfCudaOp;
+
+typedef enum BfCudaLeafKind {
+  BF_CUDA_LEAF_DENSE = 0,    /* BfMatDenseComplex / BfMatDenseReal: m x k values, row stride ld */
+  BF_CUDA_LEAF_IDENTITY = 1, /* BfMatIdentity: m == k, no values (src/mat_identity.c:149-199) */
+  BF_CUDA_LEAF_DIAG = 2      /* BfMatDiagReal: min(m,k) REAL values d[i] (src/mat_diag_real.c:168) */
+} BfCudaLeafKind;
+
+/* Leaf property bits, same meaning as BfMatProps TRANS / CONJ (include/bf/mat.h:30-39).  When
+ * TRANS is set, `val` holds the k x m STORED matrix and the leaf acts as its transpose.  As in
+ * the reference's getCblasTranspose (src/mat_dense_complex.c:27-35) a complex leaf with either
+ * bit set acts as the CONJUGATE transpose. */
+#define BF_CUDA_LEAF_TRANS 2u
+#define BF_CUDA_LEAF_CONJ 4u
+
+enum { BF_CUDA_BUF_X = 0, BF_CUDA_BUF_Y = 1, BF_CUDA_BUF_FIRST_TEMP = 2 };
+
+/* One leaf of the flattened operator.  m x k is the shape the leaf ACTS with. */
+typedef struct BfCudaRawOp {
+  int32_t kind;   /* BfCudaLeafKind */
+  uint32_t flags; /* BF_CUDA_LEAF_TRANS | BF_CUDA_LEAF_CONJ */
+  int64_t inBuf;  /* virtual buffer read */
+  int64_t inOff;  /* first row read */
+  int64_t outBuf; /* virtual buffer accumulated into */
+  int64_t outOff; /* first row written */
+  int64_t m;      /* rows produced */
+  int64_t k;      /* rows consumed */
+  int64_t ld;     /* row stride of the STORED matrix, in elements (>= stored column count) */
+  const void *val; /* host pointer to stored element (0,0); NULL = "no host values": the pool is
+                      left for bfCudaPlanFillSynthetic (benchmarks on synthetic factors) */
+} BfCudaRawOp;
+
+typedef struct BfCudaPlanDesc {
+  int32_t abiVersion;     /* BF_CUDA_ABI_VERSION */
+  int32_t dtype;          /* BfCudaDtype of every dense leaf and of X, Y */
+  int64_t numRows;        /* rows of A  == rows of buffer 1 (Y) */
+  int64_t numCols;        /* cols of A  == rows of buffer 0 (X) */
+  int64_t numBufs;        /* >= 2 */
+  const int64_t *bufRows; /* [numBufs] rows of every virtual buffer */
+  int64_t numOps;
+  const BfCudaRawOp *ops; /* [numOps], in the reference's traversal order: this order IS the
+                             summation order used for every output row (deterministic) */
+  int32_t device;         /* CUDA device ordinal, -1 = current device */
+  int32_t buildTranspose; /* nonzero: also compile the T / H direction */
+} BfCudaPlanDesc;
+
+typedef struct BfCudaPlan BfCudaPlan; /* opaque */
+
+typedef struct BfCudaPlanInfo {
+  int32_t dtype;
+  int32_t device;
+  int64_t numRows, numCols;
+  int64_t numOps;            /* raw ops */
+  int64_t numEntries;        /* E = sum over dense leaves of m*k */
+  int64_t numStagesN;        /* kernel stages per forward apply */
+  int64_t numStagesT;        /* ... per transposed apply (0 if not built) */
+  int64_t numItemsN;         /* output segments over all forward stages */
+  int64_t numTilesN;         /* block pieces over all forward stages */
+  int64_t poolBytes;         /* packed factor values resident in HBM */
+  int64_t tableBytes;        /* index tables resident in HBM */
+  int64_t workspaceRowsN;    /* rows of intermediate workspace per RHS column (forward) */
+  int64_t workspaceRowsT;
+  int64_t maxTileK;          /* widest tile after splitting */
+  int64_t maxItemRows;       /* tallest output segment after splitting */
+} BfCudaPlanInfo;
+
+/* ---- life cycle -------------------------------------------------------------------------- */
+
+/* Compile + upload.  Host value pointers in `desc` are only read during this call. */
+BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **plan);
+BfCudaStatus bfCudaPlanDestroy(BfCudaPlan *plan);
+BfCudaStatus bfCudaPlanGetInfo(const BfCudaPlan *plan, BfCudaPlanInfo *info);
+
+/* Fill the value pool on the device with a reproducible pseudo-random pattern
+ * (|entries| ~ scale / sqrt(k) so that repeated levels stay O(1)); used by benchmarks whose
+ * raw ops carry val == NULL.  The same pattern is produced on the host by
+ * bfCudaSyntheticValue so a CPU checker can regenerate any block. */
+BfCudaStatus bfCudaPlanFillSynthetic(BfCudaPlan *plan, uint64_t seed);
+/* Value of pool element `poolIndex` (real part if part == 0, imaginary if 1) of an op with k
+ * consumed rows under bfCudaPlanFillSynthetic(seed). */
+double bfCudaSyntheticValue(uint64_t seed, int64_t poolIndex, int32_t part, int64_t k);
+/* Pool element offset at which raw op `opIndex`'s stored element (0,0) lives, and its pool row
+ * stride (ops are re-packed contiguously: stride == stored column count). */
+BfCudaStatus bfCudaPlanGetOpPoolOffset(const BfCudaPlan *plan, int64_t opIndex,
+                                       int64_t *poolOffset, int64_t *poolLd);
+
+/* Optional caller-side permutations fused into the first gather / last scatter
+ * (reference callers do them as separate passes: examples/simple/helm2_bie.c:70-81,139).
+ * Semantics follow bfVecRealPermute / bfMatDenseComplexPermuteRows (out[perm[i]] = in[i]):
+ *   inPerm  (length numCols, may be NULL): the operand the plan sees is P_in applied to X,
+ *            i.e. Xp[inPerm[i], :] = X[i, :]
+ *   outPerm (length numRows, may be NULL): the caller receives Yp with Yp[outPerm[i], :] = Y[i, :]
+ * Both must be bijections; checked, BF_CUDA_ERROR_INVALID_ARGUMENT otherwise. */
+BfCudaStatus bfCudaPlanSetPerms(BfCudaPlan *plan, const int64_t *inPerm, const int64_t *outPerm);
+
+/* ---- apply --------------------------------------------------------------------------------- */
+
+/* Device-resident apply (the timed entry point).  d_x: (numCols x nrhs) for OP_N, (numRows x
+ * nrhs) for OP_T / OP_H; row-major, row strides ldx / ldy in ELEMENTS (>= nrhs).  `stream` is a
+ * cudaStream_t passed as void* (NULL = the plan's own stream).  Asynchronous w.r.t. the host. */
+BfCudaStatus bfCudaApplyDevice(BfCudaPlan *plan, int32_t op, const void *d_x, int64_t ldx,
+                               int64_t nrhs, void *d_y, int64_t ldy, void *stream);
+
+/* Host-buffer apply: H2D of X, apply, D2H of Y, synchronous.  x / y are ordinary host memory
+ * (the reference's malloc'ed BfMatDenseComplex::data / BfVecReal::data). */
+BfCudaStatus bfCudaApplyHost(BfCudaPlan *plan, int32_t op, const void *x, int64_t ldx,
+                             int64_t nrhs, void *y, int64_t ldy);
+
+/* Number of kernel launches the last apply on this plan issued (bench.py's gpu_launches). */
+int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *plan);
+
+/* Per-stage device time of the last bfCudaApplyDevice call made with profiling enabled.
+ * ms must hold numStages floats. */
+BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *plan, int32_t enable);
+BfCudaStatus bfCudaPlanGetStageTimes(BfCudaPlan *plan, float *ms, int64_t capacity,
+                                     int64_t *numStages);
+
+/* ---- persistence ----------------------------------------------------------------------------
+ * A flat little-endian file holding the raw ops + values, so a factorization that took the host
+ * an hour to build is built once (the reference has bfMatDump writers but no reader,
+ * src/mat.c:67-73). */
+BfCudaStatus bfCudaRawOpsSave(const BfCudaPlanDesc *desc, const char *path);
+/* Loads into one malloc'ed arena; free with bfCudaRawOpsFree. */
+BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **desc);
+void bfCudaRawOpsFree(BfCudaPlanDesc *desc);
+
+/* ---- misc ---------------------------------------------------------------------------------- */
+const char *bfCudaStatusString(BfCudaStatus status);
+const char *bfCudaLastErrorMessage(void); /* thread-local, human-readable detail */
+int32_t bfCudaAbiVersion(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BF_CUDA_H */

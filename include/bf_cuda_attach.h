@@ -1,0 +1,56 @@
+/* bf_cuda_attach.h — the reference-facing half of the drop-in: walks a `BfMat *` tree of the
+ * reference library and routes bfMatMul / bfMatMulVec / bfMatRmul / bfMatRmulVec on that object
+ * to the GPU plan by swapping the object's public vtable pointer (include/bf/mat.h:187-188).
+ *
+ * This header needs the reference's headers on the include path (-I<reference>/include) and is
+ * meant to be compiled INTO (or next to) libbutterfly; bf_cuda.h alone is reference-free.
+ * INTEGRATION.md shows the two lines a maintainer adds.
+ *
+ * Interfaces replaced on an attached object (signatures identical, include/bf/mat.h:90-95):
+ *   BfMat *Mul    (BfMat const *A, BfMat const *X)   src/mat_product.c:211, mat_block_dense.c:512 ...
+ *   BfVec *MulVec (BfMat const *A, BfVec const *x)   src/mat_product.c:247, mat_block_dense.c:574 ...
+ *   BfMat *Rmul   (BfMat const *A, BfMat const *X)   (computes X A)  src/mat_product.c:282
+ *   BfVec *RmulVec(BfMat const *A, BfVec const *x)   (computes A^T x) src/mat_product.c:312
+ *   BfSize NumBytes(BfMat const *A)                  unchanged value (forwards to the original)
+ *   void   Delete (BfMat **A)                        destroys the plan, then the original Delete
+ */
+#ifndef BF_CUDA_ATTACH_H
+#define BF_CUDA_ATTACH_H
+
+#include <bf/mat.h>
+#include <bf/perm.h>
+
+#include "bf_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct BfCudaAttachOpts {
+  int32_t device;         /* CUDA device ordinal, -1 = current */
+  int32_t buildTranspose; /* also compile A^T / A^H (needed by Rmul / RmulVec) */
+} BfCudaAttachOpts;
+
+/* Flatten `A` into raw ops (bf_cuda.h).  Values are NOT copied: ops point into the leaves of
+ * `A`, which must outlive the returned descriptor's use.  Supported nodes: MatProduct,
+ * MatBlockDense, MatBlockDiag, MatBlockCoo, MatSum, MatDenseComplex, MatDenseReal, MatIdentity,
+ * MatDiagReal, MatZero.  Anything else (MatPerm has no Mul in the reference either,
+ * src/mat_perm.c:53-61) -> BF_CUDA_ERROR_NOT_IMPLEMENTED. */
+BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **desc);
+void bfCudaFlattenFree(BfCudaPlanDesc *desc);
+
+/* Flatten + compile + upload + swap the vtable.  The plan is a snapshot: in-place edits of `A`
+ * (bfMatScaleCols, bfMatAddInplace ...) after attaching are not seen; detach, edit, re-attach. */
+BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts);
+/* Restore the original vtable and free the plan.  No-op error if `A` is not attached. */
+BfCudaStatus bfCudaMatDetach(BfMat *A);
+/* The plan behind an attached object (NULL if not attached); borrowed. */
+BfCudaPlan *bfCudaMatGetPlan(BfMat const *A);
+/* Fuse the caller-side tree-order permutations (bfMatPermuteRows before / after the apply,
+ * examples/simple/helm2_bie.c:70-81,139) into an attached object's plan. */
+BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *outPerm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BF_CUDA_ATTACH_H */
