@@ -107,6 +107,43 @@ class PlanInfo(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class DebugTables(C.Structure):
+    """struct BfCudaDebugTables (include/bf_cuda_debug.h)"""
+
+    _fields_ = [
+        ("dtype", C.c_int32),
+        ("op", C.c_int32),
+        ("numStages", C.c_int32),
+        ("numQueues", C.c_int32),
+        ("rowsIn", C.c_int64),
+        ("rowsOut", C.c_int64),
+        ("wsRows", C.c_int64),
+        ("numItems", C.c_int64),
+        ("numTiles", C.c_int64),
+        ("stageItemBegin", C.POINTER(C.c_int64)),
+        ("stageTileBegin", C.POINTER(C.c_int64)),
+        ("items", C.c_void_p),
+        ("tiles", C.c_void_p),
+        ("tilePool16", C.POINTER(C.c_uint64)),
+        ("qItemBegin", C.POINTER(C.c_uint32)),
+        ("qTileBegin", C.POINTER(C.c_uint32)),
+        ("qPool16", C.POINTER(C.c_uint64)),
+        ("tileOp", C.POINTER(C.c_int64)),
+        ("tileRow0", C.POINTER(C.c_int32)),
+        ("tileCol0", C.POINTER(C.c_int32)),
+        ("pool16", C.c_uint64),
+        ("pool", C.c_void_p),
+        ("owner", C.c_void_p),
+    ]
+
+
+ITEM_DTYPE = np.dtype([("outAddr", "<u4"), ("tileBegin", "<u4"), ("rows", "<u2"), ("flags", "<u2"), ("numTiles", "<u4")])
+TILE_DTYPE = np.dtype([("inAddr", "<u4"), ("kc", "<u2"), ("rows", "<u2")])
+KC_IDENTITY, KC_DIAG = 0xFFFF, 0xFFFE
+ITEM_ACCUMULATE = 1
+SPACE_X, SPACE_Y, SPACE_W = 0, 1, 2
+ROW_MASK = (1 << 30) - 1
+
 # every symbol include/bf_cuda.h declares; tests check that the .so exports all of them
 EXPORTED_SYMBOLS = [
     "bfCudaPlanCreate",
@@ -114,13 +151,14 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanGetInfo",
     "bfCudaPlanFillSynthetic",
     "bfCudaSyntheticValue",
-    "bfCudaPlanGetOpPoolOffset",
+    "bfCudaSyntheticDiagValue",
     "bfCudaPlanSetPerms",
     "bfCudaApplyDevice",
     "bfCudaApplyHost",
     "bfCudaPlanLastLaunchCount",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
+    "bfCudaPlanGetStageEntries",
     "bfCudaRawOpsSave",
     "bfCudaRawOpsLoad",
     "bfCudaRawOpsFree",
@@ -128,6 +166,7 @@ EXPORTED_SYMBOLS = [
     "bfCudaLastErrorMessage",
     "bfCudaAbiVersion",
 ]
+DEBUG_EXPORTED_SYMBOLS = ["bfCudaDebugCompile", "bfCudaDebugFree"]
 ATTACH_EXPORTED_SYMBOLS = [
     "bfCudaFlatten",
     "bfCudaFlattenFree",
@@ -168,10 +207,16 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaPlanGetInfo.restype = i32
     lib.bfCudaPlanFillSynthetic.argtypes = [vp, u64]
     lib.bfCudaPlanFillSynthetic.restype = i32
-    lib.bfCudaSyntheticValue.argtypes = [u64, i64, i32, i64]
+    lib.bfCudaSyntheticValue.argtypes = [u64, i64, i64, i32, i64]
     lib.bfCudaSyntheticValue.restype = C.c_double
-    lib.bfCudaPlanGetOpPoolOffset.argtypes = [vp, i64, C.POINTER(i64), C.POINTER(i64)]
-    lib.bfCudaPlanGetOpPoolOffset.restype = i32
+    lib.bfCudaSyntheticDiagValue.argtypes = [u64, i64, i64]
+    lib.bfCudaSyntheticDiagValue.restype = C.c_double
+    lib.bfCudaPlanGetStageEntries.argtypes = [vp, i32, C.POINTER(i64), i64, C.POINTER(i64)]
+    lib.bfCudaPlanGetStageEntries.restype = i32
+    lib.bfCudaDebugCompile.argtypes = [C.POINTER(PlanDesc), i32, i32, C.POINTER(C.POINTER(DebugTables))]
+    lib.bfCudaDebugCompile.restype = i32
+    lib.bfCudaDebugFree.argtypes = [C.POINTER(DebugTables)]
+    lib.bfCudaDebugFree.restype = None
     lib.bfCudaPlanSetPerms.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
     lib.bfCudaPlanSetPerms.restype = i32
     lib.bfCudaApplyDevice.argtypes = [vp, i32, vp, i64, i64, vp, i64, vp]

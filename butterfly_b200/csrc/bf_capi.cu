@@ -1,0 +1,438 @@
+// bf_capi.cu — the C ABI of include/bf_cuda.h: plan life cycle, device / host apply, synthetic
+// fill, profiling.  No CPU fallback anywhere: every entry point that computes needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "bf_cuda.h"
+#include "bf_kernels.cuh"
+#include "bf_plan.hpp"
+
+using namespace bfc;
+
+namespace {
+thread_local std::string g_lastError;
+BfCudaStatus fail(BfCudaStatus st, const std::string &msg) { g_lastError = msg; return st; }
+#define BF_CUDA_TRY(expr)                                                                     \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      BfCudaStatus st_ = e_ == cudaErrorMemoryAllocation ? BF_CUDA_ERROR_OUT_OF_MEMORY       \
+                                                          : BF_CUDA_ERROR_RUNTIME;            \
+      return fail(st_, std::string(#expr) + ": " + cudaGetErrorString(e_));                  \
+    }                                                                                         \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) return;
+    ok = prev == dev || cudaSetDevice(dev) == cudaSuccess;
+    if (prev == dev) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct DevDirection {
+  bool built = false;
+  Direction host;
+  // all stages concatenated; per-stage element offsets below
+  DevItem *items = nullptr;
+  DevTile *tiles = nullptr;
+  uint32_t *qItemBegin = nullptr, *qTileBegin = nullptr;
+  uint64_t *qPool16 = nullptr;
+  unsigned char *pool = nullptr;
+  std::vector<size_t> itemOff, tileOff; // per stage
+  int64_t tableBytes = 0;
+  void release() {
+    cudaFree(items); cudaFree(tiles); cudaFree(qItemBegin); cudaFree(qTileBegin); cudaFree(qPool16); cudaFree(pool);
+    items = nullptr; tiles = nullptr; qItemBegin = qTileBegin = nullptr; qPool16 = nullptr; pool = nullptr;
+    built = false;
+  }
+};
+} // namespace
+
+struct BfCudaPlan {
+  int device = 0;
+  int numSMs = 148;
+  int dtype = BF_CUDA_REAL_F64;
+  int64_t numRows = 0, numCols = 0, numOps = 0;
+  DevDirection dir[3];
+  cudaStream_t stream = nullptr;
+  // scratch: [workspace | staged X], (re)grown on demand
+  unsigned char *scratch = nullptr;
+  size_t scratchBytes = 0;
+  // host-API I/O buffers
+  unsigned char *ioX = nullptr, *ioY = nullptr;
+  size_t ioXBytes = 0, ioYBytes = 0;
+  // fused caller-side permutations (scatter form) and their inverses
+  int32_t *inPerm = nullptr, *outPerm = nullptr, *invInPerm = nullptr, *invOutPerm = nullptr;
+  int64_t lastLaunches = 0;
+  bool profiling = false;
+  std::vector<cudaEvent_t> events;
+  int64_t lastStages = 0;
+  size_t maxScratchBytes = size_t(24) << 30;
+};
+
+static BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
+  Direction &D = dd.host;
+  const size_t nS = D.stages.size();
+  const size_t Q = (size_t)D.numQueues;
+  size_t nI = 0, nT = 0;
+  dd.itemOff.assign(nS + 1, 0);
+  dd.tileOff.assign(nS + 1, 0);
+  for (size_t s = 0; s < nS; ++s) {
+    dd.itemOff[s] = nI; dd.tileOff[s] = nT;
+    nI += D.stages[s].items.size(); nT += D.stages[s].tiles.size();
+  }
+  dd.itemOff[nS] = nI; dd.tileOff[nS] = nT;
+  BF_CUDA_TRY(cudaMalloc(&dd.items, std::max<size_t>(nI, 1) * sizeof(DevItem)));
+  BF_CUDA_TRY(cudaMalloc(&dd.tiles, std::max<size_t>(nT, 1) * sizeof(DevTile)));
+  BF_CUDA_TRY(cudaMalloc(&dd.qItemBegin, nS * (Q + 1) * sizeof(uint32_t)));
+  BF_CUDA_TRY(cudaMalloc(&dd.qTileBegin, nS * (Q + 1) * sizeof(uint32_t)));
+  BF_CUDA_TRY(cudaMalloc(&dd.qPool16, nS * (Q + 1) * sizeof(uint64_t)));
+  dd.tableBytes = (int64_t)(nI * sizeof(DevItem) + nT * sizeof(DevTile) + nS * (Q + 1) * 16);
+  for (size_t s = 0; s < nS; ++s) {
+    const Stage &S = D.stages[s];
+    if (!S.items.empty())
+      BF_CUDA_TRY(cudaMemcpy(dd.items + dd.itemOff[s], S.items.data(), S.items.size() * sizeof(DevItem), cudaMemcpyHostToDevice));
+    if (!S.tiles.empty())
+      BF_CUDA_TRY(cudaMemcpy(dd.tiles + dd.tileOff[s], S.tiles.data(), S.tiles.size() * sizeof(DevTile), cudaMemcpyHostToDevice));
+    BF_CUDA_TRY(cudaMemcpy(dd.qItemBegin + s * (Q + 1), S.qItemBegin.data(), (Q + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    BF_CUDA_TRY(cudaMemcpy(dd.qTileBegin + s * (Q + 1), S.qTileBegin.data(), (Q + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    BF_CUDA_TRY(cudaMemcpy(dd.qPool16 + s * (Q + 1), S.qPool16.data(), (Q + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice));
+  }
+  const size_t poolBytes = (size_t)D.pool16 * 16 + 256; // slack: nothing reads it, keeps zero-size plans valid
+  BF_CUDA_TRY(cudaMalloc(&dd.pool, poolBytes));
+  bool anyVal = false;
+  for (const DirOp &d : D.ops) if (d.val) { anyVal = true; break; }
+  if (anyVal) {
+    // pack stage by stage through a bounded host buffer
+    size_t maxStage = 0;
+    for (const Stage &S : D.stages) maxStage = std::max(maxStage, (size_t)(S.poolEnd16 - S.poolBegin16) * 16);
+    std::unique_ptr<unsigned char[]> hostBuf(new (std::nothrow) unsigned char[std::max<size_t>(maxStage, 16)]);
+    if (!hostBuf) return fail(BF_CUDA_ERROR_OUT_OF_MEMORY, "host staging buffer for the value pool");
+    for (size_t s = 0; s < nS; ++s) {
+      const Stage &S = D.stages[s];
+      const size_t bytes = (size_t)(S.poolEnd16 - S.poolBegin16) * 16;
+      if (!bytes) continue;
+      std::memset(hostBuf.get(), 0, bytes);
+      packPool(D, s, s + 1, hostBuf.get());
+      BF_CUDA_TRY(cudaMemcpy(dd.pool + S.poolBegin16 * 16, hostBuf.get(), bytes, cudaMemcpyHostToDevice));
+    }
+  } else {
+    BF_CUDA_TRY(cudaMemset(dd.pool, 0, poolBytes));
+  }
+  dd.built = true;
+  return BF_CUDA_OK;
+}
+
+extern "C" {
+
+int32_t bfCudaAbiVersion(void) { return BF_CUDA_ABI_VERSION; }
+const char *bfCudaLastErrorMessage(void) { return g_lastError.c_str(); }
+const char *bfCudaStatusString(BfCudaStatus s) {
+  switch (s) {
+  case BF_CUDA_OK: return "ok";
+  case BF_CUDA_ERROR_INVALID_ARGUMENT: return "invalid argument";
+  case BF_CUDA_ERROR_NOT_IMPLEMENTED: return "not implemented";
+  case BF_CUDA_ERROR_OUT_OF_MEMORY: return "out of memory";
+  case BF_CUDA_ERROR_RUNTIME: return "CUDA runtime error";
+  case BF_CUDA_ERROR_NO_DEVICE: return "no usable CUDA device (there is no CPU fallback)";
+  case BF_CUDA_ERROR_IO: return "file error";
+  case BF_CUDA_ERROR_INCOMPATIBLE_SHAPES: return "incompatible shapes";
+  }
+  return "unknown status";
+}
+
+BfCudaStatus bfCudaPlanDestroy(BfCudaPlan *P) {
+  if (!P) return BF_CUDA_OK;
+  DeviceGuard g(P->device);
+  if (P->stream) cudaStreamSynchronize(P->stream);
+  for (auto &d : P->dir) d.release();
+  cudaFree(P->scratch); cudaFree(P->ioX); cudaFree(P->ioY);
+  cudaFree(P->inPerm); cudaFree(P->outPerm); cudaFree(P->invInPerm); cudaFree(P->invOutPerm);
+  for (cudaEvent_t e : P->events) cudaEventDestroy(e);
+  if (P->stream) cudaStreamDestroy(P->stream);
+  delete P;
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **out) {
+  if (!desc || !out) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
+  *out = nullptr;
+  if (desc->abiVersion != BF_CUDA_ABI_VERSION) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "ABI version mismatch");
+  if (desc->dtype != BF_CUDA_REAL_F64 && desc->dtype != BF_CUDA_COMPLEX_F64)
+    return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "unknown dtype");
+  int nDev = 0;
+  if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0) {
+    cudaGetLastError();
+    return fail(BF_CUDA_ERROR_NO_DEVICE, "no CUDA device visible; this library has no CPU fallback");
+  }
+  int dev = desc->device;
+  if (dev < 0) BF_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev >= nDev) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "device ordinal out of range");
+  DeviceGuard g(dev);
+  if (!g.ok) return fail(BF_CUDA_ERROR_RUNTIME, "cudaSetDevice failed");
+  cudaDeviceProp prop;
+  BF_CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major < 10) return fail(BF_CUDA_ERROR_NO_DEVICE, "device is not sm_100-class; kernels are built for sm_100a only");
+  BF_CUDA_TRY(configureKernels());
+
+  std::unique_ptr<BfCudaPlan> P(new BfCudaPlan());
+  P->device = dev;
+  P->numSMs = prop.multiProcessorCount;
+  P->dtype = desc->dtype;
+  P->numRows = desc->numRows;
+  P->numCols = desc->numCols;
+  P->numOps = desc->numOps;
+  BF_CUDA_TRY(cudaStreamCreateWithFlags(&P->stream, cudaStreamNonBlocking));
+  const int numQueues = P->numSMs * kWarpsPerCta;
+  std::vector<int> want{BF_CUDA_OP_N};
+  if (desc->buildTranspose & 1) want.push_back(BF_CUDA_OP_T);
+  if ((desc->buildTranspose & 2) && desc->dtype == BF_CUDA_COMPLEX_F64) want.push_back(BF_CUDA_OP_H);
+  for (int op : want) {
+    std::string err;
+    BfCudaStatus st = compileDirection(*desc, op, numQueues, P->dir[op].host, err);
+    if (st == BF_CUDA_OK) st = uploadDirection(P.get(), P->dir[op]);
+    else g_lastError = err;
+    if (st != BF_CUDA_OK) { bfCudaPlanDestroy(P.release()); return st; }
+    // host value pointers are only valid during this call
+    for (DirOp &d : P->dir[op].host.ops) d.val = nullptr;
+  }
+  *out = P.release();
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanGetInfo(const BfCudaPlan *P, BfCudaPlanInfo *info) {
+  if (!P || !info) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
+  std::memset(info, 0, sizeof *info);
+  const Direction &N = P->dir[0].host;
+  info->dtype = P->dtype; info->device = P->device;
+  info->numRows = P->numRows; info->numCols = P->numCols; info->numOps = P->numOps;
+  info->numEntries = N.entries;
+  info->numStagesN = (int64_t)N.stages.size();
+  const DevDirection &T = P->dir[1].built ? P->dir[1] : P->dir[2];
+  info->numStagesT = T.built ? (int64_t)T.host.stages.size() : 0;
+  info->numItemsN = N.numItems; info->numTilesN = N.numTiles;
+  for (const auto &d : P->dir) if (d.built) { info->poolBytes += (int64_t)d.host.pool16 * 16; info->tableBytes += d.tableBytes; }
+  info->workspaceRowsN = N.wsRows;
+  info->workspaceRowsT = T.built ? T.host.wsRows : 0;
+  info->maxTileK = N.maxTileK; info->maxItemRows = N.maxItemRows;
+  return BF_CUDA_OK;
+}
+
+static BfCudaStatus uploadPerm(const int64_t *perm, int64_t n, int32_t **dFwd, int32_t **dInv) {
+  cudaFree(*dFwd); cudaFree(*dInv);
+  *dFwd = *dInv = nullptr;
+  if (!perm) return BF_CUDA_OK;
+  std::vector<int32_t> f((size_t)n), inv((size_t)n, -1);
+  for (int64_t i = 0; i < n; ++i) {
+    if (perm[i] < 0 || perm[i] >= n || inv[(size_t)perm[i]] >= 0) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "permutation is not a bijection");
+    f[(size_t)i] = (int32_t)perm[i];
+    inv[(size_t)perm[i]] = (int32_t)i;
+  }
+  BF_CUDA_TRY(cudaMalloc(dFwd, std::max<size_t>((size_t)n, 1) * 4));
+  BF_CUDA_TRY(cudaMalloc(dInv, std::max<size_t>((size_t)n, 1) * 4));
+  BF_CUDA_TRY(cudaMemcpy(*dFwd, f.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+  BF_CUDA_TRY(cudaMemcpy(*dInv, inv.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanSetPerms(BfCudaPlan *P, const int64_t *inPerm, const int64_t *outPerm) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  DeviceGuard g(P->device);
+  BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
+  BfCudaStatus st = uploadPerm(inPerm, P->numCols, &P->inPerm, &P->invInPerm);
+  if (st != BF_CUDA_OK) return st;
+  return uploadPerm(outPerm, P->numRows, &P->outPerm, &P->invOutPerm);
+}
+
+BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *P, int32_t enable) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  P->profiling = enable != 0;
+  return BF_CUDA_OK;
+}
+
+int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *P) { return P ? P->lastLaunches : 0; }
+
+BfCudaStatus bfCudaPlanGetStageTimes(BfCudaPlan *P, float *ms, int64_t capacity, int64_t *numStages) {
+  if (!P || !numStages) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
+  DeviceGuard g(P->device);
+  *numStages = P->lastStages;
+  if (!ms) return BF_CUDA_OK;
+  if ((int64_t)P->events.size() < P->lastStages + 1) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "no profiled apply recorded");
+  BF_CUDA_TRY(cudaEventSynchronize(P->events[(size_t)P->lastStages]));
+  for (int64_t s = 0; s < P->lastStages && s < capacity; ++s)
+    BF_CUDA_TRY(cudaEventElapsedTime(&ms[s], P->events[(size_t)s], P->events[(size_t)s + 1]));
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanGetStageEntries(const BfCudaPlan *P, int32_t op, int64_t *entries, int64_t capacity,
+                                       int64_t *numStages) {
+  if (!P || !numStages || op < 0 || op > 2 || !P->dir[op].built) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "direction not built");
+  const Direction &D = P->dir[op].host;
+  *numStages = (int64_t)D.stages.size();
+  for (int64_t s = 0; entries && s < *numStages && s < capacity; ++s) entries[s] = D.stages[(size_t)s].entries;
+  return BF_CUDA_OK;
+}
+
+static BfCudaStatus ensureBytes(unsigned char **p, size_t *have, size_t want) {
+  if (*have >= want) return BF_CUDA_OK;
+  cudaFree(*p);
+  *p = nullptr; *have = 0;
+  BF_CUDA_TRY(cudaMalloc(p, want));
+  *have = want;
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs,
+                               void *d_y, int64_t ldy, void *streamOpaque) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  if (op < 0 || op > 2 || !P->dir[op].built) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "direction not built (set buildTranspose)");
+  if (nrhs < 0 || (nrhs > 0 && (ldx < nrhs || ldy < nrhs))) return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "ldx / ldy smaller than nrhs");
+  if (nrhs == 0) { P->lastLaunches = 0; return BF_CUDA_OK; }
+  if (!d_x || !d_y) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null operand");
+  DeviceGuard g(P->device);
+  DevDirection &dd = P->dir[op];
+  const Direction &D = dd.host;
+  cudaStream_t stream = streamOpaque ? (cudaStream_t)streamOpaque : P->stream;
+  const bool cplx = P->dtype == BF_CUDA_COMPLEX_F64;
+  const size_t es = cplx ? 16 : 8;
+  const int ed = cplx ? 2 : 1;
+  const int32_t *scatterIn = op == BF_CUDA_OP_N ? P->inPerm : P->invOutPerm;
+  const int32_t *scatterOut = op == BF_CUDA_OP_N ? P->outPerm : P->invInPerm;
+
+  // column chunking keeps the workspace within budget
+  const size_t rowsPad = (size_t)D.wsRows + 2;
+  const size_t xRowsPad = (size_t)D.rowsIn + 2;
+  int64_t chunk = nrhs;
+  while (chunk > 1 && (rowsPad + xRowsPad) * (size_t)chunk * es > P->maxScratchBytes) chunk = (chunk + 1) / 2;
+  const size_t wsBytes = ((rowsPad * (size_t)chunk * es + 255) / 256) * 256;
+  const size_t need = wsBytes + xRowsPad * (size_t)chunk * es + 256;
+  if (P->scratchBytes < need) {
+    BF_CUDA_TRY(cudaStreamSynchronize(stream));
+    BfCudaStatus st = ensureBytes(&P->scratch, &P->scratchBytes, need);
+    if (st != BF_CUDA_OK) return st;
+  }
+  const size_t nS = D.stages.size();
+  const size_t Q = (size_t)D.numQueues;
+  if (P->profiling) {
+    while (P->events.size() < nS + 1) { cudaEvent_t e; BF_CUDA_TRY(cudaEventCreate(&e)); P->events.push_back(e); }
+  }
+  int64_t launches = 0;
+  for (int64_t c0 = 0; c0 < nrhs; c0 += chunk) {
+    const int64_t nc = std::min(chunk, nrhs - c0);
+    const unsigned char *xp = static_cast<const unsigned char *>(d_x) + (size_t)c0 * es;
+    unsigned char *yp = static_cast<unsigned char *>(d_y) + (size_t)c0 * es;
+    StageLaunch a{};
+    a.pool = dd.pool;
+    a.base[kSpaceY] = yp; a.ld[kSpaceY] = ldy;
+    a.base[kSpaceW] = P->scratch; a.ld[kSpaceW] = nc;
+    a.outPerm = scatterOut;
+    a.numQueues = D.numQueues; a.nrhs = (int)nc; a.colBegin = 0;
+    // The 1-RHS kernel bulk-copies operand segments: they must be dense and 16-byte aligned (real
+    // segments may start 8 bytes into a 16-byte window, so they always go through the padded copy).
+    const bool needStage = scatterIn != nullptr || (nc == 1 && (!cplx || ldx != 1 || (reinterpret_cast<uintptr_t>(xp) & 15)));
+    if (needStage) {
+      unsigned char *xs = P->scratch + wsBytes;
+      cudaError_t e = launchPermuteRows(reinterpret_cast<const double *>(xp), ldx, reinterpret_cast<double *>(xs), nc,
+                                        scatterIn, D.rowsIn, (int)nc, ed, stream);
+      if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("permute launch: ") + cudaGetErrorString(e));
+      ++launches;
+      a.base[kSpaceX] = xs; a.ld[kSpaceX] = nc;
+    } else {
+      a.base[kSpaceX] = const_cast<unsigned char *>(xp); a.ld[kSpaceX] = ldx;
+    }
+    for (size_t s = 0; s < nS; ++s) {
+      if (P->profiling && c0 == 0) BF_CUDA_TRY(cudaEventRecord(P->events[s], stream));
+      a.items = dd.items + dd.itemOff[s];
+      a.tiles = dd.tiles + dd.tileOff[s];
+      a.qItemBegin = dd.qItemBegin + s * (Q + 1);
+      a.qTileBegin = dd.qTileBegin + s * (Q + 1);
+      a.qPool16 = dd.qPool16 + s * (Q + 1);
+      cudaError_t e = nc == 1 ? launchGemvStage(P->dtype, a, P->numSMs, stream) : launchWideStage(P->dtype, a, P->numSMs, stream);
+      if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("stage launch: ") + cudaGetErrorString(e));
+      ++launches;
+    }
+    if (P->profiling && c0 == 0) BF_CUDA_TRY(cudaEventRecord(P->events[nS], stream));
+  }
+  P->lastStages = (int64_t)nS;
+  P->lastLaunches = launches;
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaApplyHost(BfCudaPlan *P, int32_t op, const void *x, int64_t ldx, int64_t nrhs, void *y,
+                             int64_t ldy) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  if (op < 0 || op > 2 || !P->dir[op].built) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "direction not built (set buildTranspose)");
+  if (nrhs < 0 || (nrhs > 0 && (ldx < nrhs || ldy < nrhs))) return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "ldx / ldy smaller than nrhs");
+  if (nrhs == 0) return BF_CUDA_OK;
+  if (!x || !y) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null operand");
+  DeviceGuard g(P->device);
+  const Direction &D = P->dir[op].host;
+  const size_t es = P->dtype == BF_CUDA_COMPLEX_F64 ? 16 : 8;
+  const size_t rowBytes = (size_t)nrhs * es;
+  BfCudaStatus st = ensureBytes(&P->ioX, &P->ioXBytes, std::max<size_t>((size_t)D.rowsIn * rowBytes, 16));
+  if (st != BF_CUDA_OK) return st;
+  st = ensureBytes(&P->ioY, &P->ioYBytes, std::max<size_t>((size_t)D.rowsOut * rowBytes, 16));
+  if (st != BF_CUDA_OK) return st;
+  if (D.rowsIn > 0)
+    BF_CUDA_TRY(cudaMemcpy2DAsync(P->ioX, rowBytes, x, (size_t)ldx * es, rowBytes, (size_t)D.rowsIn, cudaMemcpyHostToDevice, P->stream));
+  st = bfCudaApplyDevice(P, op, P->ioX, nrhs, nrhs, P->ioY, nrhs, P->stream);
+  if (st != BF_CUDA_OK) return st;
+  if (D.rowsOut > 0)
+    BF_CUDA_TRY(cudaMemcpy2DAsync(y, (size_t)ldy * es, P->ioY, rowBytes, rowBytes, (size_t)D.rowsOut, cudaMemcpyDeviceToHost, P->stream));
+  BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanFillSynthetic(BfCudaPlan *P, uint64_t seed) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  DeviceGuard g(P->device);
+  for (auto &dd : P->dir) {
+    if (!dd.built) continue;
+    const Direction &D = dd.host;
+    for (const Stage &S : D.stages) {
+      const size_t nT = S.tiles.size();
+      if (!nT) continue;
+      std::vector<FillPiece> fp(nT);
+      for (size_t t = 0; t < nT; ++t) {
+        const DirOp &d = D.ops[(size_t)S.pieces[t].op];
+        FillPiece &f = fp[t];
+        f.pool16 = S.tilePool16[t];
+        f.rawIndex = d.rawIndex;
+        f.row0 = S.pieces[t].row0; f.col0 = S.pieces[t].col0;
+        f.storedCols = (int32_t)d.storedCols;
+        f.rows = S.tiles[t].rows; f.kc = S.tiles[t].kc;
+        f.swapRC = d.swapRC; f.conj = d.conj; f.kind = (uint8_t)d.kind; f.pad = 0;
+        // scale by the contraction length of the leaf as it acts in the forward direction
+        f.scale = syntheticScale(D.op == BF_CUDA_OP_N ? d.k : d.m);
+      }
+      FillPiece *dp = nullptr;
+      BF_CUDA_TRY(cudaMalloc(&dp, nT * sizeof(FillPiece)));
+      cudaError_t e = cudaMemcpy(dp, fp.data(), nT * sizeof(FillPiece), cudaMemcpyHostToDevice);
+      if (e == cudaSuccess) e = launchFillSynthetic(P->dtype, dd.pool, dp, (long long)nT, seed, P->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(P->stream);
+      cudaFree(dp);
+      if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("synthetic fill: ") + cudaGetErrorString(e));
+    }
+  }
+  return BF_CUDA_OK;
+}
+
+double bfCudaSyntheticValue(uint64_t seed, int64_t opIndex, int64_t storedLinear, int32_t part, int64_t k) {
+  return syntheticValue(seed, opIndex, storedLinear, part, syntheticScale(k));
+}
+double bfCudaSyntheticDiagValue(uint64_t seed, int64_t opIndex, int64_t i) {
+  return 1.0 + 0.5 * syntheticValue(seed, opIndex, i, 0, 1.0);
+}
+
+} // extern "C"

@@ -1,0 +1,493 @@
+// bf_kernels.cu — hand-written sm_100a kernels for the butterfly apply.
+//
+// Two stage kernels consume the same stage-major tables and the same packed value pool
+// (bf_plan.hpp):
+//   bfGemvStage  nrhs == 1.  HBM-bandwidth bound (0.5 flop/B complex, 0.25 real).  One warp owns
+//                one static work queue and streams its contiguous span of the pool through a
+//                private ring of shared-memory slots filled by TMA bulk copies (cp.async.bulk +
+//                mbarrier complete_tx).  The operand segment of every tile rides on the same
+//                mbarrier.  8 (complex) / 16 (real) lanes cooperate on a row: conflict-free 128-byte
+//                LDS phases, operand held in registers, one shuffle reduction per ITEM (not per
+//                tile), one coalesced store.  No atomics: summation order is the plan's order.
+//   bfWideStage  nrhs >= 2.  One CTA owns kWarpsPerCta consecutive queues; RHS columns across
+//                threads, A tiles TMA-staged and read as LDS broadcasts, fp64 FMA pipe bound.
+//
+// Replaces the per-leaf cblas_zgemm / cblas_dgemv calls of the reference
+// (src/mat_dense_complex.c:1754, src/mat_dense_real.c:1358,1428) and the block loops around
+// them (src/mat_block_coo.c:404-418, src/mat_block_diag.c:387-399, src/mat_block_dense.c:534-566).
+#include "bf_kernels.cuh"
+
+namespace bfc {
+
+// ---- PTX helpers ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smemU32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t policyEvictFirst() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+// 1-D TMA bulk copy global -> shared, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void bulkLoad(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulkLoadHint(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void fenceBarrierInit() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t tileBytes(int es, uint32_t rows, uint32_t kc) {
+  if (kc == kKcIdentity) return 0u;
+  if (kc == kKcDiag) return (rows * 8u + 15u) & ~15u;
+  return (rows * kc * (uint32_t)es + 15u) & ~15u;
+}
+
+template <bool CPLX> struct Scalar;
+template <> struct Scalar<true> {
+  using T = double2;
+  static __device__ __forceinline__ T zero() { return make_double2(0.0, 0.0); }
+  static __device__ __forceinline__ void fma(T &acc, const T a, const T x) {
+    acc.x = ::fma(a.x, x.x, acc.x); acc.x = ::fma(-a.y, x.y, acc.x);
+    acc.y = ::fma(a.x, x.y, acc.y); acc.y = ::fma(a.y, x.x, acc.y);
+  }
+  static __device__ __forceinline__ void fmaReal(T &acc, double d, const T x) { acc.x = ::fma(d, x.x, acc.x); acc.y = ::fma(d, x.y, acc.y); }
+  static __device__ __forceinline__ T add(T a, T b) { return make_double2(a.x + b.x, a.y + b.y); }
+  static __device__ __forceinline__ T shflXor(T v, int m) { return make_double2(__shfl_xor_sync(0xffffffffu, v.x, m), __shfl_xor_sync(0xffffffffu, v.y, m)); }
+  static __device__ __forceinline__ T shfl(T v, int src) { return make_double2(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src)); }
+};
+template <> struct Scalar<false> {
+  using T = double;
+  static __device__ __forceinline__ T zero() { return 0.0; }
+  static __device__ __forceinline__ void fma(T &acc, const T a, const T x) { acc = ::fma(a, x, acc); }
+  static __device__ __forceinline__ void fmaReal(T &acc, double d, const T x) { acc = ::fma(d, x, acc); }
+  static __device__ __forceinline__ T add(T a, T b) { return a + b; }
+  static __device__ __forceinline__ T shflXor(T v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+  static __device__ __forceinline__ T shfl(T v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+};
+
+__device__ __forceinline__ unsigned char *rowPtr(const StageLaunch &a, uint32_t addr, int es) {
+  const uint32_t sp = addr >> 30;
+  return a.base[sp] + (long long)(addr & kRowMask) * a.ld[sp] * es;
+}
+
+// ---- 1-RHS stage kernel ---------------------------------------------------------------------------
+template <bool CPLX>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid_constant__ StageLaunch a) {
+  using S = Scalar<CPLX>;
+  using T = typename S::T;
+  constexpr int ES = CPLX ? 16 : 8;
+  constexpr int G = CPLX ? 8 : 16; // lanes per row: one 128-byte LDS phase per row chunk
+  constexpr int RPP = 32 / G;      // rows per pass
+  constexpr int P = 8;             // passes: RPP * P == max item rows
+  constexpr int KT = 8;            // register chunks of G columns: G * KT == max tile columns
+  static_assert(RPP * P == (CPLX ? kMaxRowsComplex : kMaxRowsReal), "item rows");
+  static_assert(G * KT == (CPLX ? kMaxKcComplex : kMaxKcReal), "tile columns");
+  static_assert((CPLX ? kMaxKcComplex * 16 : kMaxKcReal * 8 + 16) <= kGemvXBytes, "x slot");
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char *ring = smem + warp * (kGemvSlots * kGemvSlotBytes);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kWarpsPerCta * kGemvSlots * kGemvSlotBytes) + warp * kGemvSlots;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kGemvSlots; ++s) mbarInit(smemU32(&bars[s]), 1);
+    fenceBarrierInit();
+  }
+  __syncthreads();
+
+  const int q = blockIdx.x * kWarpsPerCta + warp;
+  if (q >= a.numQueues) return;
+  const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
+  const uint32_t tEnd = a.qTileBegin[q + 1];
+  if (iBeg == iEnd) return;
+  const uint64_t pol = policyEvictFirst();
+
+  // producer (lane 0 issues; every lane tracks the same scalars) and consumer cursors
+  uint32_t pT = a.qTileBegin[q], pSeq = 0, cSeq = 0;
+  const unsigned char *pPool = a.pool + a.qPool16[q] * 16ull;
+  const unsigned char *cPool = pPool;
+
+  auto produce = [&]() {
+    while (pT < tEnd) {
+      const DevTile t = a.tiles[pT];
+      ++pT;
+      const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
+      const unsigned char *src = pPool;
+      pPool += bytes;
+      if (t.kc >= kKcDiag) continue; // identity / diagonal tiles are read directly by the consumer
+      if (lane == 0) {
+        const uint32_t slot = pSeq % kGemvSlots;
+        const uint32_t dst = smemU32(ring + slot * kGemvSlotBytes);
+        const uint32_t bar = smemU32(&bars[slot]);
+        const unsigned char *xsrc = rowPtr(a, t.inAddr, ES);
+        uint32_t xb;
+        if (CPLX) {
+          xb = (uint32_t)t.kc * 16u;
+        } else { // 8-byte elements: copy from the enclosing 16-byte aligned window
+          const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(xsrc) & 8u);
+          xsrc -= shift;
+          xb = (shift + (uint32_t)t.kc * 8u + 15u) & ~15u;
+        }
+        mbarExpectTx(bar, bytes + xb);
+        bulkLoadHint(dst, src, bytes, bar, pol);
+        bulkLoad(dst + kTileBytes, xsrc, xb, bar);
+      }
+      ++pSeq;
+      return;
+    }
+  };
+#pragma unroll 1
+  for (int s = 0; s < kGemvSlots; ++s) produce();
+
+  const int g = lane / G, l = lane % G;
+#pragma unroll 1
+  for (uint32_t i = iBeg; i < iEnd; ++i) {
+    const DevItem it = a.items[i];
+    const int rows = it.rows;
+    T acc[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) acc[p] = S::zero();
+    T extra = S::zero();
+
+#pragma unroll 1
+    for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
+      const DevTile tl = a.tiles[t];
+      const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
+      if (tl.kc >= kKcDiag) {
+        if (lane < rows) {
+          const uint32_t sp = tl.inAddr >> 30;
+          const T xv = *reinterpret_cast<const T *>(rowPtr(a, tl.inAddr, ES) + (long long)lane * a.ld[sp] * ES);
+          const double d = tl.kc == kKcDiag ? reinterpret_cast<const double *>(cPool)[lane] : 1.0;
+          S::fmaReal(extra, d, xv);
+        }
+        cPool += bytes;
+        continue;
+      }
+      const int kc = tl.kc;
+      const uint32_t slot = cSeq % kGemvSlots;
+      const unsigned char *As = ring + slot * kGemvSlotBytes;
+      const unsigned char *xsB = As + kTileBytes;
+      if (!CPLX) xsB += reinterpret_cast<uintptr_t>(rowPtr(a, tl.inAddr, ES)) & 8u;
+      mbarWait(smemU32(&bars[slot]), (cSeq / kGemvSlots) & 1u);
+
+      const T *xs = reinterpret_cast<const T *>(xsB);
+      T xr[KT];
+#pragma unroll
+      for (int tt = 0; tt < KT; ++tt) {
+        const int j = tt * G + l;
+        xr[tt] = (tt * G < kc && j < kc) ? xs[j] : S::zero();
+      }
+      const T *A = reinterpret_cast<const T *>(As);
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        if (p * RPP < rows) {
+          const int r = p * RPP + g;
+          const bool rv = r < rows;
+          const T *Ar = A + r * kc;
+#pragma unroll
+          for (int tt = 0; tt < KT; ++tt) {
+            if (tt * G < kc) {
+              const int j = tt * G + l;
+              if (rv && j < kc) S::fma(acc[p], Ar[j], xr[tt]);
+            }
+          }
+        }
+      }
+      __syncwarp();
+      produce(); // refill the slot just drained
+      ++cSeq;
+      cPool += bytes;
+    }
+
+    // one reduction per item: over the G lanes of a row, then row r -> lane r for a coalesced store
+    T out = S::zero();
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      if (p * RPP < rows) {
+        T v = acc[p];
+#pragma unroll
+        for (int off = G / 2; off > 0; off >>= 1) v = S::add(v, S::shflXor(v, off));
+        v = S::shfl(v, (lane % RPP) * G);
+        if (lane / RPP == p) out = v;
+      }
+    }
+    out = S::add(out, extra);
+    if (lane < rows) {
+      const uint32_t sp = it.outAddr >> 30;
+      long long row = (long long)(it.outAddr & kRowMask) + lane;
+      if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
+      T *dst = reinterpret_cast<T *>(a.base[sp] + row * a.ld[sp] * ES);
+      if (it.flags & kItemAccumulate) out = S::add(out, *dst);
+      *dst = out;
+    }
+  }
+}
+
+// ---- many-RHS stage kernel ------------------------------------------------------------------------
+// Thread (rg, c): column c of the RHS chunk, rows rg, rg + NRG, ... of every item.  The A tile is a
+// warp-uniform LDS broadcast; the operand row X[j, :] is one coalesced global load per thread and is
+// reused for RT rows (4 DFMA each for complex), so the inner loop is fp64-pipe bound.
+template <bool CPLX, int NC>
+__global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_constant__ StageLaunch a) {
+  using S = Scalar<CPLX>;
+  using T = typename S::T;
+  constexpr int ES = CPLX ? 16 : 8;
+  constexpr int R = CPLX ? kMaxRowsComplex : kMaxRowsReal;
+  constexpr int NRG = kWideThreads / NC;
+  static_assert(NRG >= 1 && NRG <= R && R % NRG == 0, "row groups");
+  constexpr int RT = R / NRG;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kWideSlots * kTileBytes);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kWideSlots; ++s) mbarInit(smemU32(&bars[s]), 1);
+    fenceBarrierInit();
+  }
+  __syncthreads();
+
+  const int q0 = blockIdx.x * kWarpsPerCta;
+  if (q0 >= a.numQueues) return;
+  const int q1 = min(q0 + kWarpsPerCta, a.numQueues);
+  const uint32_t iBeg = a.qItemBegin[q0], iEnd = a.qItemBegin[q1];
+  const uint32_t tEnd = a.qTileBegin[q1];
+  if (iBeg == iEnd) return;
+  const uint64_t pol = policyEvictFirst();
+
+  const int c = tid % NC, rg = tid / NC;
+  const long long col = (long long)a.colBegin + (long long)blockIdx.y * NC + c;
+  const bool colOk = col < a.nrhs;
+
+  uint32_t pT = a.qTileBegin[q0], pSeq = 0, cSeq = 0;
+  const unsigned char *pPool = a.pool + a.qPool16[q0] * 16ull;
+  const unsigned char *cPool = pPool;
+  auto produce = [&]() {
+    while (pT < tEnd) {
+      const DevTile t = a.tiles[pT];
+      ++pT;
+      const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
+      const unsigned char *src = pPool;
+      pPool += bytes;
+      if (t.kc >= kKcDiag) continue;
+      if (tid == 0) {
+        const uint32_t slot = pSeq % kWideSlots;
+        const uint32_t bar = smemU32(&bars[slot]);
+        mbarExpectTx(bar, bytes);
+        bulkLoadHint(smemU32(smem + slot * kTileBytes), src, bytes, bar, pol);
+      }
+      ++pSeq;
+      return;
+    }
+  };
+#pragma unroll 1
+  for (int s = 0; s < kWideSlots; ++s) produce();
+
+#pragma unroll 1
+  for (uint32_t i = iBeg; i < iEnd; ++i) {
+    const DevItem it = a.items[i];
+    const int rows = it.rows;
+    T acc[RT];
+#pragma unroll
+    for (int u = 0; u < RT; ++u) acc[u] = S::zero();
+
+#pragma unroll 1
+    for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
+      const DevTile tl = a.tiles[t];
+      const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
+      const uint32_t sp = tl.inAddr >> 30;
+      const long long ldIn = a.ld[sp];
+      const T *xp = reinterpret_cast<const T *>(a.base[sp]) + (long long)(tl.inAddr & kRowMask) * ldIn + col;
+      if (tl.kc >= kKcDiag) {
+        const double *dg = reinterpret_cast<const double *>(cPool);
+#pragma unroll
+        for (int u = 0; u < RT; ++u) {
+          const int r = u * NRG + rg;
+          if (r < rows && colOk) S::fmaReal(acc[u], tl.kc == kKcDiag ? dg[r] : 1.0, xp[(long long)r * ldIn]);
+        }
+        cPool += bytes;
+        continue;
+      }
+      const int kc = tl.kc;
+      const uint32_t slot = cSeq % kWideSlots;
+      const T *A = reinterpret_cast<const T *>(smem + slot * kTileBytes);
+      mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
+
+      int j = 0;
+#pragma unroll 1
+      for (; j + 4 <= kc; j += 4) {
+        T x0 = S::zero(), x1 = S::zero(), x2 = S::zero(), x3 = S::zero();
+        if (colOk) {
+          x0 = xp[(long long)(j + 0) * ldIn]; x1 = xp[(long long)(j + 1) * ldIn];
+          x2 = xp[(long long)(j + 2) * ldIn]; x3 = xp[(long long)(j + 3) * ldIn];
+        }
+#pragma unroll
+        for (int u = 0; u < RT; ++u) {
+          const int r = u * NRG + rg;
+          if (r < rows) {
+            const T *Ar = A + r * kc + j;
+            S::fma(acc[u], Ar[0], x0); S::fma(acc[u], Ar[1], x1);
+            S::fma(acc[u], Ar[2], x2); S::fma(acc[u], Ar[3], x3);
+          }
+        }
+      }
+#pragma unroll 1
+      for (; j < kc; ++j) {
+        const T x0 = colOk ? xp[(long long)j * ldIn] : S::zero();
+#pragma unroll
+        for (int u = 0; u < RT; ++u) {
+          const int r = u * NRG + rg;
+          if (r < rows) S::fma(acc[u], A[r * kc + j], x0);
+        }
+      }
+      __syncthreads(); // every thread is done with this slot
+      produce();
+      ++cSeq;
+      cPool += bytes;
+    }
+
+    if (colOk) {
+      const uint32_t sp = it.outAddr >> 30;
+      const long long ldOut = a.ld[sp];
+#pragma unroll
+      for (int u = 0; u < RT; ++u) {
+        const int r = u * NRG + rg;
+        if (r < rows) {
+          long long row = (long long)(it.outAddr & kRowMask) + r;
+          if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
+          T *dst = reinterpret_cast<T *>(a.base[sp]) + row * ldOut + col;
+          T v = acc[u];
+          if (it.flags & kItemAccumulate) v = S::add(v, *dst);
+          *dst = v;
+        }
+      }
+    }
+  }
+}
+
+// ---- staging copy with the caller-side row permutation fused in ---------------------------------
+__global__ void bfPermuteRows(const double *__restrict__ src, long long ldSrc, double *__restrict__ dst,
+                              long long ldDst, const int32_t *__restrict__ perm, long long rows,
+                              int rowDoubles, int elemDoubles) {
+  // one thread per double of the row block; consecutive threads walk along a row
+  const long long total = rows * rowDoubles;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long i = idx / rowDoubles, c = idx % rowDoubles;
+    const long long o = perm ? (long long)perm[i] : i;
+    dst[o * ldDst * elemDoubles + c] = src[i * ldSrc * elemDoubles + c];
+  }
+}
+
+cudaError_t launchPermuteRows(const double *src, long long ldSrc, double *dst, long long ldDst,
+                              const int32_t *perm, long long rows, int nrhs, int elemDoubles,
+                              cudaStream_t stream) {
+  const long long total = rows * nrhs * elemDoubles;
+  if (total == 0) return cudaSuccess;
+  const int threads = 256;
+  const long long blocks = (total + threads - 1) / threads;
+  bfPermuteRows<<<(unsigned)(blocks > 148 * 32 ? 148 * 32 : blocks), threads, 0, stream>>>(
+      src, ldSrc, dst, ldDst, perm, rows, nrhs * elemDoubles, elemDoubles);
+  return cudaGetLastError();
+}
+
+// ---- synthetic pool fill --------------------------------------------------------------------------
+__global__ void bfFillSynthetic(int cplx, unsigned char *pool, const FillPiece *__restrict__ pieces,
+                                long long numPieces, uint64_t seed) {
+  for (long long pi = blockIdx.x; pi < numPieces; pi += gridDim.x) {
+    const FillPiece p = pieces[pi];
+    double *dst = reinterpret_cast<double *>(pool + p.pool16 * 16ull);
+    if (p.kc == kKcIdentity) continue;
+    if (p.kc == kKcDiag) {
+      for (int r = threadIdx.x; r < p.rows; r += blockDim.x)
+        dst[r] = 1.0 + 0.5 * syntheticValue(seed, p.rawIndex, p.row0 + r, 0, 1.0);
+      continue;
+    }
+    const int n = (int)p.rows * (int)p.kc;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+      const int r = e / p.kc, c = e % p.kc;
+      const long long pr = p.row0 + r, qc = p.col0 + c;
+      const long long sr = p.swapRC ? qc : pr, sc = p.swapRC ? pr : qc;
+      const long long lin = sr * p.storedCols + sc;
+      if (cplx) {
+        const double re = syntheticValue(seed, p.rawIndex, lin, 0, p.scale);
+        const double im = syntheticValue(seed, p.rawIndex, lin, 1, p.scale);
+        dst[2 * e] = re;
+        dst[2 * e + 1] = p.conj ? -im : im;
+      } else {
+        dst[e] = syntheticValue(seed, p.rawIndex, lin, 0, p.scale);
+      }
+    }
+  }
+}
+
+cudaError_t launchFillSynthetic(int dtype, unsigned char *pool, const FillPiece *pieces, long long numPieces,
+                                uint64_t seed, cudaStream_t stream) {
+  if (numPieces == 0) return cudaSuccess;
+  const long long blocks = numPieces < 148 * 16 ? numPieces : 148 * 16;
+  bfFillSynthetic<<<(unsigned)blocks, 128, 0, stream>>>(dtype == BF_CUDA_COMPLEX_F64, pool, pieces, numPieces, seed);
+  return cudaGetLastError();
+}
+
+// ---- launchers ----------------------------------------------------------------------------------------
+cudaError_t configureKernels() {
+  cudaError_t e;
+  e = cudaFuncSetAttribute(bfGemvStage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfGemvStage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaSuccess;
+}
+
+cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int /*numSMs*/, cudaStream_t stream) {
+  const int ctas = (a.numQueues + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (ctas == 0) return cudaSuccess;
+  if (dtype == BF_CUDA_COMPLEX_F64) bfGemvStage<true><<<ctas, kWarpsPerCta * 32, kGemvSmemBytes, stream>>>(a);
+  else bfGemvStage<false><<<ctas, kWarpsPerCta * 32, kGemvSmemBytes, stream>>>(a);
+  return cudaGetLastError();
+}
+
+template <bool CPLX, int NC>
+static cudaError_t launchWideT(const StageLaunch &a, int ncols, cudaStream_t stream) {
+  const int ctas = (a.numQueues + kWarpsPerCta - 1) / kWarpsPerCta;
+  dim3 grid((unsigned)ctas, (unsigned)((ncols + NC - 1) / NC));
+  bfWideStage<CPLX, NC><<<grid, kWideThreads, kWideSmemBytes, stream>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launchWideStage(int dtype, const StageLaunch &a, int /*numSMs*/, cudaStream_t stream) {
+  const int ncols = a.nrhs - a.colBegin;
+  if (ncols <= 0 || a.numQueues == 0) return cudaSuccess;
+  if (dtype == BF_CUDA_COMPLEX_F64) {
+    if (ncols > 128) return launchWideT<true, 256>(a, ncols, stream);
+    if (ncols > 64) return launchWideT<true, 128>(a, ncols, stream);
+    if (ncols > 32) return launchWideT<true, 64>(a, ncols, stream);
+    if (ncols > 16) return launchWideT<true, 32>(a, ncols, stream);
+    return launchWideT<true, 16>(a, ncols, stream);
+  }
+  if (ncols > 128) return launchWideT<false, 256>(a, ncols, stream);
+  if (ncols > 64) return launchWideT<false, 128>(a, ncols, stream);
+  if (ncols > 32) return launchWideT<false, 64>(a, ncols, stream);
+  return launchWideT<false, 32>(a, ncols, stream);
+}
+
+} // namespace bfc

@@ -1,0 +1,63 @@
+// bf_kernels.cuh — launch interface between the C ABI (bf_capi.cu) and the sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "bf_plan.hpp"
+
+namespace bfc {
+
+// Everything one stage launch needs; passed by value as a __grid_constant__ kernel parameter.
+struct StageLaunch {
+  const DevItem *items;
+  const DevTile *tiles;
+  const uint32_t *qItemBegin; // [numQueues + 1]
+  const uint32_t *qTileBegin; // [numQueues + 1]
+  const uint64_t *qPool16;    // [numQueues + 1]
+  const unsigned char *pool;  // byte 0 of the value pool
+  unsigned char *base[3];     // X, Y, workspace
+  long long ld[3];            // row strides in ELEMENTS
+  const int32_t *outPerm;     // NULL, or: row r of the result is stored at row outPerm[r]
+  int numQueues;
+  int nrhs;
+  int colBegin;               // first RHS column this launch handles (wide kernel)
+};
+
+// Shared-memory geometry of the 1-RHS kernel (one ring of kGemvSlots slots per warp).
+constexpr int kGemvSlots = 3;
+constexpr int kGemvXBytes = 1056;                        // x segment: 64 c128 / 128 f64 (+16 B slack)
+constexpr int kGemvSlotBytes = kTileBytes + kGemvXBytes; // 9248
+constexpr int kGemvSmemBytes = kWarpsPerCta * kGemvSlots * (kGemvSlotBytes + 8) + 128;
+
+// Wide (many-RHS) kernel: CTA-wide ring of A tiles; one CTA owns kWarpsPerCta consecutive queues.
+constexpr int kWideSlots = 4;
+constexpr int kWideThreads = 512;
+constexpr int kWideSmemBytes = kWideSlots * (kTileBytes + 8) + 128;
+
+// 1 RHS: y = A x, one warp per queue, TMA-staged tiles, shuffle reductions.
+cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);
+// nrhs >= 2: one CTA per kWarpsPerCta queues, columns across threads.
+cudaError_t launchWideStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);
+cudaError_t configureKernels(); // opt in to the large dynamic shared memory carve-outs
+
+// dst[(perm ? perm[i] : i) * ldDst + c] = src[i * ldSrc + c]  (elements of elemDoubles doubles).
+// Fuses the caller-side bfMatPermuteRows (src/mat_dense_complex.c:741-774) into the staging copy.
+cudaError_t launchPermuteRows(const double *src, long long ldSrc, double *dst, long long ldDst,
+                              const int32_t *perm, long long rows, int nrhs, int elemDoubles,
+                              cudaStream_t stream);
+
+// Synthetic pool fill (bfCudaPlanFillSynthetic): one entry per tile.
+struct FillPiece {
+  uint64_t pool16;    // where the tile lives
+  int64_t rawIndex;   // raw op
+  int32_t row0, col0; // piece origin in the direction's acting matrix
+  int32_t storedCols;
+  uint16_t rows, kc;
+  uint8_t swapRC, conj, kind, pad;
+  double scale;
+};
+cudaError_t launchFillSynthetic(int dtype, unsigned char *pool, const FillPiece *pieces, long long numPieces,
+                                uint64_t seed, cudaStream_t stream);
+
+} // namespace bfc

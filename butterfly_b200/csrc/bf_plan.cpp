@@ -1,0 +1,370 @@
+// bf_plan.cpp — plan compiler: raw ops -> stage-major items / tiles / packed pool.  Host only.
+#include "bf_plan.hpp"
+
+#include <algorithm>
+#include <climits>
+#include <complex>
+#include <cstring>
+#include <numeric>
+
+namespace bfc {
+
+int kcForRows(int dtype, int rows) {
+  const bool cplx = dtype == BF_CUDA_COMPLEX_F64;
+  const int lanesPerRow = cplx ? 8 : 16;
+  const int cap = cplx ? kMaxKcComplex : kMaxKcReal;
+  int kc = kTileBytes / (rows * elemBytes(dtype));
+  kc -= kc % lanesPerRow;
+  return std::max(lanesPerRow, std::min(cap, kc));
+}
+
+static bool leafStoredTransposed(const BfCudaRawOp &o, bool cplx) {
+  // getCblasTranspose (src/mat_dense_complex.c:27-35): either bit => conjugate transpose;
+  // real leaves: TRANS => transpose (src/mat_dense_real.c:1345-1358).
+  if (cplx) return (o.flags & (BF_CUDA_LEAF_TRANS | BF_CUDA_LEAF_CONJ)) != 0;
+  return (o.flags & BF_CUDA_LEAF_TRANS) != 0;
+}
+
+namespace {
+struct Frag {       // one (leaf, elementary output interval) incidence
+  int32_t stage;
+  int64_t elem;     // global elementary-interval id (ordered by buffer, then row)
+  int64_t seq;      // position in the direction's op order == summation order
+};
+struct Elem {
+  int64_t buf, start, len;
+  int32_t minStage;
+};
+} // namespace
+
+BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQueues, Direction &D,
+                              std::string &err) {
+  const bool cplx = desc.dtype == BF_CUDA_COMPLEX_F64;
+  const bool rev = op != BF_CUDA_OP_N;
+  if (op == BF_CUDA_OP_H && !cplx) { err = "OP_H on a real plan"; return BF_CUDA_ERROR_INVALID_ARGUMENT; }
+  if (desc.numBufs < 2 || !desc.bufRows || (desc.numOps > 0 && !desc.ops)) {
+    err = "malformed descriptor"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  }
+  if (desc.bufRows[BF_CUDA_BUF_X] != desc.numCols || desc.bufRows[BF_CUDA_BUF_Y] != desc.numRows) {
+    err = "buffer 0 / 1 must have numCols / numRows rows"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  }
+  D = Direction();
+  D.op = op;
+  D.dtype = desc.dtype;
+  D.numQueues = numQueues;
+  D.inBufId = rev ? BF_CUDA_BUF_Y : BF_CUDA_BUF_X;
+  D.outBufId = rev ? BF_CUDA_BUF_X : BF_CUDA_BUF_Y;
+  D.rowsIn = desc.bufRows[D.inBufId];
+  D.rowsOut = desc.bufRows[D.outBufId];
+  const int64_t nB = desc.numBufs, nOps = desc.numOps;
+
+  // ---- 1. leaves as they act in this direction, in processing order -------------------------
+  D.ops.reserve((size_t)nOps);
+  for (int64_t n = 0; n < nOps; ++n) {
+    const int64_t ri = rev ? nOps - 1 - n : n;
+    const BfCudaRawOp &o = desc.ops[ri];
+    if (o.inBuf < 0 || o.inBuf >= nB || o.outBuf < 0 || o.outBuf >= nB || o.m < 0 || o.k < 0 ||
+        o.inOff < 0 || o.outOff < 0 || o.inOff + o.k > desc.bufRows[o.inBuf] ||
+        o.outOff + o.m > desc.bufRows[o.outBuf] || o.inBuf == o.outBuf) {
+      err = "op " + std::to_string(ri) + ": range outside its buffers"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+    }
+    if (o.kind != BF_CUDA_LEAF_DENSE && o.kind != BF_CUDA_LEAF_IDENTITY && o.kind != BF_CUDA_LEAF_DIAG) {
+      err = "op " + std::to_string(ri) + ": unknown leaf kind"; return BF_CUDA_ERROR_NOT_IMPLEMENTED;
+    }
+    if (o.m == 0 || o.k == 0) continue;
+    DirOp d{};
+    d.kind = o.kind;
+    d.rawIndex = ri;
+    d.val = o.val;
+    d.ld = o.ld;
+    const bool st = o.kind == BF_CUDA_LEAF_DENSE && leafStoredTransposed(o, cplx);
+    // acting(a,b) = st ? conj(stored(b,a)) : stored(a,b);  N: D = acting, T: D = acting^T, H: acting^H
+    d.swapRC = (uint8_t)(st ^ rev);
+    d.conj = (uint8_t)(cplx && (st ^ (op == BF_CUDA_OP_H)));
+    d.storedCols = st ? o.m : o.k;
+    if (o.kind == BF_CUDA_LEAF_DENSE && o.ld < d.storedCols) {
+      err = "op " + std::to_string(ri) + ": ld smaller than the stored column count"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+    }
+    d.inBuf = rev ? o.outBuf : o.inBuf;  d.inOff = rev ? o.outOff : o.inOff;
+    d.outBuf = rev ? o.inBuf : o.outBuf; d.outOff = rev ? o.inOff : o.outOff;
+    d.m = rev ? o.k : o.m;               d.k = rev ? o.m : o.k;
+    if (o.kind != BF_CUDA_LEAF_DENSE) { // identity / diagonal act on min(m,k) rows; the rest is zero
+      d.m = d.k = std::min(o.m, o.k);
+      d.swapRC = 0; d.conj = 0; d.storedCols = 1;
+    }
+    D.ops.push_back(d);
+  }
+
+  // ---- 2. stages: an op runs once every writer of its operand buffer has run ------------------
+  std::vector<int32_t> level((size_t)nB, 0), firstW((size_t)nB, INT_MAX), lastW((size_t)nB, -1);
+  std::vector<uint8_t> wasRead((size_t)nB, 0);
+  int32_t numStages = 1;
+  for (DirOp &d : D.ops) {
+    if (d.outBuf == D.inBufId) { err = "an op writes the operand buffer"; return BF_CUDA_ERROR_INVALID_ARGUMENT; }
+    if (d.inBuf == D.outBufId) { err = "an op reads the result buffer"; return BF_CUDA_ERROR_INVALID_ARGUMENT; }
+    if (wasRead[d.outBuf]) { err = "buffer " + std::to_string(d.outBuf) + " written after being read (ops not in dependency order)"; return BF_CUDA_ERROR_INVALID_ARGUMENT; }
+    wasRead[d.inBuf] = 1;
+    d.stage = level[d.inBuf];
+    level[d.outBuf] = std::max(level[d.outBuf], d.stage + 1);
+    firstW[d.outBuf] = std::min(firstW[d.outBuf], d.stage);
+    lastW[d.outBuf] = std::max(lastW[d.outBuf], d.stage);
+    numStages = std::max(numStages, d.stage + 1);
+    if (d.kind == BF_CUDA_LEAF_DENSE) D.entries += d.m * d.k;
+  }
+  for (const DirOp &d : D.ops)
+    if (d.inBuf != D.inBufId && lastW[d.inBuf] < 0) {
+      err = "an op reads buffer " + std::to_string(d.inBuf) + " which nothing writes"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+    }
+  D.stages.assign((size_t)numStages, Stage());
+
+  // ---- 3. workspace: ping-pong arenas keyed by the parity of the stage that READS a buffer ----
+  // A temp written only at stage s-1 and read at stage s is live during s-1 and s; temps read at
+  // s+1 are born at s.  Two arenas (even / odd read stage) therefore never alias live data.
+  // Buffers written over several stages (a MatProduct factor that itself contains products) get
+  // dedicated rows.
+  D.wsOffset.assign((size_t)nB, -1);
+  {
+    std::vector<int64_t> perStage((size_t)numStages + 2, 0);
+    int64_t dedicated = 0;
+    std::vector<int64_t> off((size_t)nB, 0);
+    std::vector<int8_t> cls((size_t)nB, -1); // 0/1 arena parity, 2 dedicated, -1 unused
+    for (int64_t b = 0; b < nB; ++b) {
+      if (b == D.inBufId || b == D.outBufId) continue;
+      if (lastW[b] < 0) continue; // never written: never read either unless it is all zeros
+      const int64_t rows = (desc.bufRows[b] + 1) & ~int64_t(1); // even, keeps 16-byte alignment for real
+      if (firstW[b] == lastW[b]) {
+        const int32_t rs = level[b];
+        cls[b] = (int8_t)(rs & 1);
+        off[b] = perStage[rs];
+        perStage[rs] += rows;
+      } else {
+        cls[b] = 2;
+        off[b] = dedicated;
+        dedicated += rows;
+      }
+    }
+    int64_t arena[2] = {0, 0};
+    for (int32_t s = 0; s < numStages + 2; ++s) arena[s & 1] = std::max(arena[s & 1], perStage[s]);
+    for (int64_t b = 0; b < nB; ++b) {
+      if (cls[b] == 0) D.wsOffset[b] = off[b];
+      else if (cls[b] == 1) D.wsOffset[b] = arena[0] + off[b];
+      else if (cls[b] == 2) D.wsOffset[b] = arena[0] + arena[1] + off[b];
+    }
+    D.wsRows = arena[0] + arena[1] + dedicated;
+    if (D.wsRows > (int64_t)kRowMask || D.rowsIn > (int64_t)kRowMask || D.rowsOut > (int64_t)kRowMask) {
+      err = "operator too large for 30-bit row addresses"; return BF_CUDA_ERROR_NOT_IMPLEMENTED;
+    }
+  }
+  auto addrOf = [&](int64_t buf, int64_t row) -> uint32_t {
+    if (buf == D.inBufId) return packAddr(kSpaceX, row);
+    if (buf == D.outBufId) return packAddr(kSpaceY, row);
+    return packAddr(kSpaceW, D.wsOffset[buf] + row);
+  };
+
+  // ---- 4. elementary output intervals and (leaf, interval) incidences -------------------------
+  // Every output buffer is cut at all outOff / outOff + m of the leaves that write it; a leaf
+  // covers a run of whole elementary intervals, and rows of a row-major leaf stay contiguous
+  // under row splitting.  An item is an elementary interval (cut again into <= R rows) at one
+  // stage; it stores (first stage to touch those rows) or accumulates (later stages).
+  const int64_t nD = (int64_t)D.ops.size();
+  std::vector<int64_t> byOut((size_t)nD);
+  std::iota(byOut.begin(), byOut.end(), int64_t(0));
+  std::sort(byOut.begin(), byOut.end(), [&](int64_t a, int64_t b) {
+    const DirOp &x = D.ops[a], &y = D.ops[b];
+    if (x.outBuf != y.outBuf) return x.outBuf < y.outBuf;
+    if (x.outOff != y.outOff) return x.outOff < y.outOff;
+    return a < b;
+  });
+  std::vector<Elem> elems;
+  std::vector<Frag> frags;
+  frags.reserve((size_t)nD + 16);
+  std::vector<int64_t> bps;
+  auto pushGap = [&](int64_t buf, int64_t a, int64_t b) { // rows [a,b) of buf that no leaf writes
+    if (b <= a) return;
+    const int32_t st = firstW[buf] == INT_MAX ? 0 : firstW[buf];
+    elems.push_back(Elem{buf, a, b - a, st});
+    frags.push_back(Frag{st, (int64_t)elems.size() - 1, -1});
+  };
+  {
+    int64_t g = 0;
+    std::vector<uint8_t> seen((size_t)nB, 0);
+    while (g < nD) {
+      const int64_t buf = D.ops[byOut[g]].outBuf;
+      int64_t h = g;
+      bps.clear();
+      while (h < nD && D.ops[byOut[h]].outBuf == buf) {
+        const DirOp &d = D.ops[byOut[h]];
+        bps.push_back(d.outOff);
+        bps.push_back(d.outOff + d.m);
+        ++h;
+      }
+      std::sort(bps.begin(), bps.end());
+      bps.erase(std::unique(bps.begin(), bps.end()), bps.end());
+      seen[buf] = 1;
+      pushGap(buf, 0, bps.front());
+      const int64_t e0 = (int64_t)elems.size();
+      for (size_t i = 0; i + 1 < bps.size(); ++i) elems.push_back(Elem{buf, bps[i], bps[i + 1] - bps[i], INT_MAX});
+      for (int64_t i = g; i < h; ++i) {
+        const DirOp &d = D.ops[byOut[i]];
+        const int64_t lo = std::lower_bound(bps.begin(), bps.end(), d.outOff) - bps.begin();
+        const int64_t hi = std::lower_bound(bps.begin(), bps.end(), d.outOff + d.m) - bps.begin();
+        for (int64_t e = lo; e < hi; ++e) {
+          frags.push_back(Frag{d.stage, e0 + e, byOut[i]});
+          elems[(size_t)(e0 + e)].minStage = std::min(elems[(size_t)(e0 + e)].minStage, d.stage);
+        }
+      }
+      const int64_t e1 = (int64_t)elems.size();
+      for (int64_t e = e0; e < e1; ++e)
+        if (elems[(size_t)e].minStage == INT_MAX) { // hole between two leaves
+          elems[(size_t)e].minStage = firstW[buf];
+          frags.push_back(Frag{firstW[buf], e, -1});
+        }
+      pushGap(buf, bps.back(), desc.bufRows[buf]);
+      g = h;
+    }
+    // nothing writes the result at all: it is all zeros
+    for (int64_t b = 0; b < nB; ++b)
+      if (!seen[b] && b == D.outBufId) pushGap(b, 0, desc.bufRows[b]);
+  }
+  std::sort(frags.begin(), frags.end(), [](const Frag &a, const Frag &b) {
+    if (a.stage != b.stage) return a.stage < b.stage;
+    if (a.elem != b.elem) return a.elem < b.elem;
+    return a.seq < b.seq;
+  });
+
+  // ---- 5. items and tiles per stage -------------------------------------------------------------
+  const int R = maxItemRows(desc.dtype);
+  for (size_t f = 0; f < frags.size();) {
+    size_t f1 = f;
+    while (f1 < frags.size() && frags[f1].stage == frags[f].stage && frags[f1].elem == frags[f].elem) ++f1;
+    const Elem &el = elems[(size_t)frags[f].elem];
+    Stage &S = D.stages[(size_t)frags[f].stage];
+    const bool zeroOnly = frags[f].seq < 0;
+    const int64_t nChunks = (el.len + R - 1) / R;
+    for (int64_t c = 0; c < nChunks; ++c) {
+      const int64_t r0 = el.len * c / nChunks, r1 = el.len * (c + 1) / nChunks;
+      const int rows = (int)(r1 - r0);
+      DevItem it{};
+      it.outAddr = addrOf(el.buf, el.start + r0);
+      it.tileBegin = (uint32_t)S.tiles.size();
+      it.rows = (uint16_t)rows;
+      it.flags = (uint16_t)((!zeroOnly && frags[f].stage > el.minStage) ? kItemAccumulate : 0);
+      if (!zeroOnly) {
+        const int KC = kcForRows(desc.dtype, rows);
+        for (size_t q = f; q < f1; ++q) {
+          const DirOp &d = D.ops[(size_t)frags[q].seq];
+          const int64_t rowInOp = el.start + r0 - d.outOff;
+          if (d.kind != BF_CUDA_LEAF_DENSE) {
+            DevTile t{addrOf(d.inBuf, d.inOff + rowInOp), d.kind == BF_CUDA_LEAF_DIAG ? kKcDiag : kKcIdentity, (uint16_t)rows};
+            S.tiles.push_back(t);
+            S.pieces.push_back(PieceRef{frags[q].seq, (int32_t)rowInOp, (int32_t)rowInOp});
+            continue;
+          }
+          const int64_t nK = (d.k + KC - 1) / KC;
+          for (int64_t kk = 0; kk < nK; ++kk) {
+            const int64_t c0 = d.k * kk / nK, c1 = d.k * (kk + 1) / nK;
+            DevTile t{addrOf(d.inBuf, d.inOff + c0), (uint16_t)(c1 - c0), (uint16_t)rows};
+            S.tiles.push_back(t);
+            S.pieces.push_back(PieceRef{frags[q].seq, (int32_t)rowInOp, (int32_t)c0});
+            D.maxTileK = std::max<int64_t>(D.maxTileK, c1 - c0);
+          }
+          S.entries += (int64_t)rows * d.k;
+        }
+      }
+      it.numTiles = (uint32_t)S.tiles.size() - it.tileBegin;
+      S.items.push_back(it);
+      D.maxItemRows = std::max<int64_t>(D.maxItemRows, rows);
+    }
+    f = f1;
+  }
+
+  // ---- 6. static work queues + pool layout -------------------------------------------------------
+  // Items of a stage are dealt, in order, to numQueues queues of nearly equal cost (bytes streamed
+  // plus a fixed charge per tile and per item).  The pool is laid out in that same order, so queue
+  // q streams the contiguous span [qPool16[q], qPool16[q+1]) of HBM.
+  uint64_t pool16 = 0;
+  for (Stage &S : D.stages) {
+    const size_t nI = S.items.size(), nT = S.tiles.size();
+    S.tilePool16.resize(nT);
+    S.poolBegin16 = pool16;
+    std::vector<uint64_t> cost(nI + 1, 0);
+    for (size_t i = 0; i < nI; ++i) {
+      const DevItem &it = S.items[i];
+      uint64_t c = 256 + 32ull * it.rows;
+      for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
+        S.tilePool16[t] = pool16;
+        const uint64_t b16 = tileBytes16(desc.dtype, S.tiles[t].rows, S.tiles[t].kc);
+        pool16 += b16;
+        c += 16 * b16 + 384;
+      }
+      cost[i + 1] = cost[i] + c;
+    }
+    S.poolEnd16 = pool16;
+    S.qItemBegin.assign((size_t)numQueues + 1, (uint32_t)nI);
+    S.qTileBegin.assign((size_t)numQueues + 1, (uint32_t)nT);
+    S.qPool16.assign((size_t)numQueues + 1, pool16);
+    const uint64_t total = cost[nI];
+    size_t i = 0;
+    for (int q = 0; q < numQueues; ++q) {
+      S.qItemBegin[(size_t)q] = (uint32_t)i;
+      S.qTileBegin[(size_t)q] = i < nI ? S.items[i].tileBegin : (uint32_t)nT;
+      S.qPool16[(size_t)q] = (i < nI && S.items[i].tileBegin < nT) ? S.tilePool16[S.items[i].tileBegin] : pool16;
+      // take items while their midpoint lies before this queue's share boundary
+      const long double bound = (long double)total * (q + 1) / numQueues;
+      while (i < nI && (long double)(cost[i] + cost[i + 1]) * 0.5L < bound) ++i;
+      if (q == numQueues - 1) i = nI;
+    }
+    // fix pool offsets of queues that begin at an item without tiles: the next tile in order
+    for (int q = numQueues - 1; q >= 0; --q) {
+      const uint32_t tb = S.qTileBegin[(size_t)q];
+      S.qPool16[(size_t)q] = tb < nT ? S.tilePool16[tb] : pool16;
+    }
+    D.numItems += (int64_t)nI;
+    D.numTiles += (int64_t)nT;
+  }
+  D.pool16 = pool16;
+  return BF_CUDA_OK;
+}
+
+// ---- value packing ------------------------------------------------------------------------------
+template <typename T> static inline T conjIf(T v, bool) { return v; }
+template <> inline std::complex<double> conjIf(std::complex<double> v, bool c) { return c ? std::conj(v) : v; }
+
+template <typename T>
+static void packStage(const Direction &dir, const Stage &S, T *base /* pool offset poolBegin16 */) {
+  const size_t nT = S.tiles.size();
+  for (size_t t = 0; t < nT; ++t) {
+    const DevTile &tl = S.tiles[t];
+    if (tl.kc == kKcIdentity) continue;
+    const PieceRef &pr = S.pieces[t];
+    const DirOp &d = dir.ops[(size_t)pr.op];
+    if (!d.val) continue;
+    char *dstBytes = reinterpret_cast<char *>(base) + 16 * (S.tilePool16[t] - S.poolBegin16);
+    if (tl.kc == kKcDiag) { // real diagonal values, also on a complex operator (src/mat_diag_real.c:168)
+      double *dst = reinterpret_cast<double *>(dstBytes);
+      const double *src = static_cast<const double *>(d.val);
+      for (int r = 0; r < tl.rows; ++r) dst[r] = src[pr.row0 + r];
+      continue;
+    }
+    T *dst = reinterpret_cast<T *>(dstBytes);
+    const T *src = static_cast<const T *>(d.val);
+    const int rows = tl.rows, kc = tl.kc;
+    for (int r = 0; r < rows; ++r)
+      for (int c = 0; c < kc; ++c) {
+        const int64_t p = pr.row0 + r, q = pr.col0 + c;
+        const int64_t sr = d.swapRC ? q : p, sc = d.swapRC ? p : q;
+        dst[(size_t)r * kc + c] = conjIf(src[sr * d.ld + sc], d.conj != 0);
+      }
+  }
+}
+
+void packPool(const Direction &dir, size_t s0, size_t s1, void *dst) {
+  for (size_t s = s0; s < s1; ++s) {
+    const Stage &S = dir.stages[s];
+    char *base = static_cast<char *>(dst) + 16 * (S.poolBegin16 - dir.stages[s0].poolBegin16);
+    if (dir.dtype == BF_CUDA_COMPLEX_F64) packStage(dir, S, reinterpret_cast<std::complex<double> *>(base));
+    else packStage(dir, S, reinterpret_cast<double *>(base));
+  }
+}
+
+} // namespace bfc

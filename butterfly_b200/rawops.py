@@ -16,19 +16,21 @@ from . import capi
 
 class RawOps:
     def __init__(self, dtype, num_rows, num_cols, buf_rows, ops, values=None):
-        """ops: structured array (capi.RAWOP_DTYPE); if `values` is given, each dense/diag op's
-        `val` field holds an ELEMENT OFFSET into `values` (resolved to pointers by desc());
-        if values is None every val must be 0 (synthetic pool)."""
+        """ops: structured array (capi.RAWOP_DTYPE); if `values` is given (a float64 array; complex
+        leaves are interleaved re, im), each dense/diag op's `val` field holds an offset IN DOUBLES
+        into `values` (resolved to pointers by desc()); if values is None every val must be 0
+        (value-less plan: the pool is filled by bfCudaPlanFillSynthetic)."""
         self.dtype = int(dtype)
         self.num_rows = int(num_rows)
         self.num_cols = int(num_cols)
         self.buf_rows = np.ascontiguousarray(buf_rows, dtype=np.int64)
         self.ops = np.ascontiguousarray(ops, dtype=capi.RAWOP_DTYPE)
-        self.values = None if values is None else np.ascontiguousarray(values)
-        if self.values is not None:
-            want = np.complex128 if self.dtype == capi.COMPLEX_F64 else np.float64
-            # diag leaves of a complex operator are REAL: they are stored as the real parts
-            assert self.values.dtype == want, (self.values.dtype, want)
+        if values is not None:
+            values = np.ascontiguousarray(values)
+            if values.dtype == np.complex128:
+                values = values.view(np.float64)
+            assert values.dtype == np.float64 and values.ndim == 1
+        self.values = values
         self._keep = None
 
     # ------------------------------------------------------------------------------------------
@@ -46,9 +48,8 @@ class RawOps:
         ops = self.ops.copy()
         if self.values is not None:
             base = self.values.ctypes.data
-            esz = self.values.itemsize
             has = ops["kind"] != capi.LEAF_IDENTITY
-            ops["val"][has] = base + ops["val"][has] * np.uint64(esz)
+            ops["val"][has] = np.uint64(base) + ops["val"][has] * np.uint64(8)
             ops["val"][~has] = 0
         else:
             assert not ops["val"].any()
@@ -76,19 +77,19 @@ class RawOps:
         ops = np.frombuffer(buf, dtype=capi.RAWOP_DTYPE).copy() if n else np.zeros(0, capi.RAWOP_DTYPE)
         buf_rows = np.ctypeslib.as_array(desc.bufRows, shape=(int(desc.numBufs),)).copy()
         cplx = desc.dtype == capi.COMPLEX_F64
-        vdt = np.complex128 if cplx else np.float64
+        e = 2 if cplx else 1
         sizes = np.zeros(n, np.int64)
         for i in range(n):
             o = ops[i]
             if o["kind"] == capi.LEAF_DENSE:
-                sizes[i] = o["m"] * o["k"]
+                sizes[i] = o["m"] * o["k"] * e
             elif o["kind"] == capi.LEAF_DIAG:
                 sizes[i] = min(o["m"], o["k"])
         offs = np.concatenate([[0], np.cumsum(sizes)])
-        pool = np.zeros(int(offs[-1]), vdt)
+        pool = np.zeros(int(offs[-1]), np.float64)
         for i in range(n):
             o = ops[i]
-            if sizes[i] == 0:
+            if sizes[i] == 0 or int(o["val"]) == 0:
                 ops["val"][i] = 0
                 continue
             if o["kind"] == capi.LEAF_DENSE:
@@ -96,11 +97,9 @@ class RawOps:
                 sr, sc = (int(o["k"]), int(o["m"])) if acts_t else (int(o["m"]), int(o["k"]))
                 ld = int(o["ld"])
                 raw = np.ctypeslib.as_array(
-                    C.cast(int(o["val"]), C.POINTER(C.c_double)),
-                    shape=((sr - 1) * ld * (2 if cplx else 1) + sc * (2 if cplx else 1),),
+                    C.cast(int(o["val"]), C.POINTER(C.c_double)), shape=(((sr - 1) * ld + sc) * e,)
                 )
-                a = raw.view(vdt)
-                blk = np.lib.stride_tricks.as_strided(a, (sr, sc), (ld * a.itemsize, a.itemsize))
+                blk = np.lib.stride_tricks.as_strided(raw, (sr, sc * e), (ld * e * 8, 8))
                 pool[offs[i] : offs[i + 1]] = blk.reshape(-1)
                 ops["ld"][i] = sc
             else:  # diag: real values

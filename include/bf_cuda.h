@@ -114,7 +114,8 @@ typedef struct BfCudaPlanDesc {
   const BfCudaRawOp *ops; /* [numOps], in the reference's traversal order: this order IS the
                              summation order used for every output row (deterministic) */
   int32_t device;         /* CUDA device ordinal, -1 = current device */
-  int32_t buildTranspose; /* nonzero: also compile the T / H direction */
+  int32_t buildTranspose; /* bit 0: also compile A^T (OP_T); bit 1: also compile A^H (OP_H,
+                             complex only).  Each extra direction holds its own packed pool. */
 } BfCudaPlanDesc;
 
 typedef struct BfCudaPlan BfCudaPlan; /* opaque */
@@ -144,18 +145,17 @@ BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **plan);
 BfCudaStatus bfCudaPlanDestroy(BfCudaPlan *plan);
 BfCudaStatus bfCudaPlanGetInfo(const BfCudaPlan *plan, BfCudaPlanInfo *info);
 
-/* Fill the value pool on the device with a reproducible pseudo-random pattern
- * (|entries| ~ scale / sqrt(k) so that repeated levels stay O(1)); used by benchmarks whose
- * raw ops carry val == NULL.  The same pattern is produced on the host by
- * bfCudaSyntheticValue so a CPU checker can regenerate any block. */
+/* Fill the value pool on the device with a reproducible pseudo-random pattern; used by
+ * benchmarks whose raw ops carry val == NULL (synthetic factors of the named size: real structure,
+ * synthetic values).  The value of STORED element (row, col) of dense raw op `opIndex` is
+ * bfCudaSyntheticValue(seed, opIndex, row * storedCols + col, part, k): uniform in
+ * [-2^-round(log2(k)/2), +...) with k the op's contraction length, so that repeated levels stay
+ * O(1).  Diagonal leaves get bfCudaSyntheticDiagValue(seed, opIndex, i) in [0.5, 1.5).  Both are
+ * integer hashes followed by one exact multiply: a CPU checker regenerates identical bits. */
 BfCudaStatus bfCudaPlanFillSynthetic(BfCudaPlan *plan, uint64_t seed);
-/* Value of pool element `poolIndex` (real part if part == 0, imaginary if 1) of an op with k
- * consumed rows under bfCudaPlanFillSynthetic(seed). */
-double bfCudaSyntheticValue(uint64_t seed, int64_t poolIndex, int32_t part, int64_t k);
-/* Pool element offset at which raw op `opIndex`'s stored element (0,0) lives, and its pool row
- * stride (ops are re-packed contiguously: stride == stored column count). */
-BfCudaStatus bfCudaPlanGetOpPoolOffset(const BfCudaPlan *plan, int64_t opIndex,
-                                       int64_t *poolOffset, int64_t *poolLd);
+double bfCudaSyntheticValue(uint64_t seed, int64_t opIndex, int64_t storedLinear, int32_t part,
+                            int64_t k);
+double bfCudaSyntheticDiagValue(uint64_t seed, int64_t opIndex, int64_t i);
 
 /* Optional caller-side permutations fused into the first gather / last scatter
  * (reference callers do them as separate passes: examples/simple/helm2_bie.c:70-81,139).
@@ -187,6 +187,9 @@ int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *plan);
 BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *plan, int32_t enable);
 BfCudaStatus bfCudaPlanGetStageTimes(BfCudaPlan *plan, float *ms, int64_t capacity,
                                      int64_t *numStages);
+/* Dense entries (sum of m*k) applied by every stage of direction `op`: the per-stage share of E. */
+BfCudaStatus bfCudaPlanGetStageEntries(const BfCudaPlan *plan, int32_t op, int64_t *entries,
+                                       int64_t capacity, int64_t *numStages);
 
 /* ---- persistence ----------------------------------------------------------------------------
  * A flat little-endian file holding the raw ops + values, so a factorization that took the host

@@ -1,0 +1,108 @@
+"""numpy interpreter of the compiled plan tables (include/bf_cuda_debug.h).  TEST CODE: it walks
+stages / items / tiles exactly as the kernels do, on NaN-initialised buffers, so that any row a
+kernel would read before it is written, any aliasing of live workspace rows and any mistake in
+tile addressing or pool packing shows up without a GPU."""
+import ctypes as C
+
+import numpy as np
+
+from butterfly_b200 import capi
+
+
+class Tables:
+    def __init__(self, raw, op=capi.OP_N, num_queues=148 * 8):
+        self.lib = capi.load_library()
+        self.raw = raw
+        self._desc = raw.desc()
+        t = C.POINTER(capi.DebugTables)()
+        capi.check(self.lib.bfCudaDebugCompile(C.byref(self._desc), op, num_queues, C.byref(t)), "bfCudaDebugCompile")
+        self._t = t
+        d = t.contents
+        self.d = d
+        nS, Q = d.numStages, d.numQueues
+        arr = lambda p, n, dt: np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_ubyte)), shape=(n * np.dtype(dt).itemsize,)).view(dt).copy() if n else np.zeros(0, dt)
+        self.stage_item = arr(d.stageItemBegin, nS + 1, np.int64)
+        self.stage_tile = arr(d.stageTileBegin, nS + 1, np.int64)
+        self.items = arr(d.items, d.numItems, capi.ITEM_DTYPE)
+        self.tiles = arr(d.tiles, d.numTiles, capi.TILE_DTYPE)
+        self.tile_pool16 = arr(d.tilePool16, d.numTiles, np.uint64)
+        self.q_item = arr(d.qItemBegin, nS * (Q + 1), np.uint32).reshape(nS, Q + 1)
+        self.q_tile = arr(d.qTileBegin, nS * (Q + 1), np.uint32).reshape(nS, Q + 1)
+        self.q_pool16 = arr(d.qPool16, nS * (Q + 1), np.uint64).reshape(nS, Q + 1)
+        self.tile_op = arr(d.tileOp, d.numTiles, np.int64)
+        self.pool = arr(d.pool, int(d.pool16) * 2, np.float64)
+        self.num_stages, self.num_queues = nS, Q
+        self.rows_in, self.rows_out, self.ws_rows = d.rowsIn, d.rowsOut, d.wsRows
+        self.cplx = d.dtype == capi.COMPLEX_F64
+
+    def close(self):
+        if self._t:
+            self.lib.bfCudaDebugFree(self._t)
+            self._t = None
+
+    def apply(self, x):
+        dt = np.complex128 if self.cplx else np.float64
+        x = np.asarray(x, dtype=dt)
+        if x.ndim == 1:
+            x = x[:, None]
+        nrhs = x.shape[1]
+        nan = np.nan * (1 + 1j) if self.cplx else np.nan
+        space = [x, np.full((self.rows_out, nrhs), nan, dt), np.full((self.ws_rows + 2, nrhs), nan, dt)]
+        e = 2 if self.cplx else 1
+        for s in range(self.num_stages):
+            i0, i1 = self.stage_item[s], self.stage_item[s + 1]
+            t0 = self.stage_tile[s]
+            # an item's reads see the state before this stage (no intra-stage dependencies allowed)
+            results = []
+            for it in self.items[i0:i1]:
+                rows = int(it["rows"])
+                acc = np.zeros((rows, nrhs), dt)
+                for t in range(t0 + int(it["tileBegin"]), t0 + int(it["tileBegin"]) + int(it["numTiles"])):
+                    tl = self.tiles[t]
+                    assert int(tl["rows"]) == rows
+                    sp, r = int(tl["inAddr"]) >> 30, int(tl["inAddr"]) & capi.ROW_MASK
+                    kc = int(tl["kc"])
+                    p0 = int(self.tile_pool16[t]) * 2
+                    if kc == capi.KC_IDENTITY:
+                        acc += space[sp][r:r + rows]
+                    elif kc == capi.KC_DIAG:
+                        acc += self.pool[p0:p0 + rows, None] * space[sp][r:r + rows]
+                    else:
+                        a = self.pool[p0:p0 + rows * kc * e]
+                        a = a.view(np.complex128) if self.cplx else a
+                        acc += a.reshape(rows, kc) @ space[sp][r:r + kc]
+                results.append(acc)
+            for it, acc in zip(self.items[i0:i1], results):
+                sp, r = int(it["outAddr"]) >> 30, int(it["outAddr"]) & capi.ROW_MASK
+                assert sp != capi.SPACE_X
+                rows = int(it["rows"])
+                if int(it["flags"]) & capi.ITEM_ACCUMULATE:
+                    space[sp][r:r + rows] += acc
+                else:
+                    space[sp][r:r + rows] = acc
+        return space[1]
+
+    def check_queues(self):
+        """Queues partition every stage's items in order; each queue's pool offset is where its
+        first tile lives; tiles are packed back to back in consumption order."""
+        for s in range(self.num_stages):
+            nI = self.stage_item[s + 1] - self.stage_item[s]
+            nT = self.stage_tile[s + 1] - self.stage_tile[s]
+            qi, qt, qp = self.q_item[s], self.q_tile[s], self.q_pool16[s]
+            assert qi[0] == 0 and qi[-1] == nI and np.all(np.diff(qi.astype(np.int64)) >= 0)
+            assert qt[0] == 0 and qt[-1] == nT and np.all(np.diff(qt.astype(np.int64)) >= 0)
+            items = self.items[self.stage_item[s]:self.stage_item[s + 1]]
+            tp = self.tile_pool16[self.stage_tile[s]:self.stage_tile[s + 1]]
+            for q in range(self.num_queues):
+                if qi[q] < nI:
+                    assert qt[q] == items[qi[q]]["tileBegin"]
+                if qt[q] < nT:
+                    assert qp[q] == tp[qt[q]]
+            # back-to-back packing
+            tl = self.tiles[self.stage_tile[s]:self.stage_tile[s + 1]]
+            es = 16 if self.cplx else 8
+            kc = tl["kc"].astype(np.int64)
+            rows = tl["rows"].astype(np.int64)
+            b16 = np.where(kc == capi.KC_IDENTITY, 0, np.where(kc == capi.KC_DIAG, (rows * 8 + 15) // 16, (rows * kc * es + 15) // 16))
+            if nT:
+                assert np.all(np.diff(tp.astype(np.int64)) == b16[:-1])

@@ -1,0 +1,67 @@
+"""CPU: the plan compiler's tables, interpreted with numpy, reproduce the oracle.  Pins stage
+assignment, item / tile row ranges, workspace aliasing, queue partition, transposition and
+conjugation and pool packing without a GPU."""
+import numpy as np
+import pytest
+
+from butterfly_b200 import capi, synth
+from oracle import portlib
+from table_interp import Tables
+
+
+def _x(rng, n, nrhs, cplx):
+    x = rng.standard_normal((n, nrhs))
+    return x + 1j * rng.standard_normal((n, nrhs)) if cplx else x
+
+
+CASES = [
+    ("hodbf_c", lambda: synth.random_hodbf(n=1500, dtype=capi.COMPLEX_F64, seed=3)),
+    ("hodbf_r", lambda: synth.random_hodbf(n=1100, dtype=capi.REAL_F64, seed=4)),
+    ("rect_r", lambda: synth.random_rect(700, 300, capi.REAL_F64, seed=5)),
+    ("rect_c", lambda: synth.random_rect(333, 517, capi.COMPLEX_F64, seed=6)),
+    ("plain_c", lambda: synth.random_hodbf(n=900, dtype=capi.COMPLEX_F64, seed=7, exotic=False)),
+]
+
+
+@pytest.mark.parametrize("name,make", CASES)
+@pytest.mark.parametrize("op", [capi.OP_N, capi.OP_T, capi.OP_H])
+def test_tables_match_oracle(name, make, op):
+    raw = make()
+    cplx = raw.dtype == capi.COMPLEX_F64
+    if op == capi.OP_H and not cplx:
+        pytest.skip("OP_H is complex only")
+    rng = np.random.default_rng(11)
+    n_in = raw.num_cols if op == capi.OP_N else raw.num_rows
+    x = _x(rng, n_in, 3, cplx)
+    y_ref = portlib.apply(raw, x, op)
+    t = Tables(raw, op, num_queues=37)
+    try:
+        t.check_queues()
+        y = t.apply(x)
+    finally:
+        t.close()
+    assert not np.isnan(y).any(), "a result row is never written"
+    err = np.linalg.norm(y - y_ref) / np.linalg.norm(y_ref)
+    assert err < 1e-13, err
+
+
+def test_queue_count_does_not_change_the_result():
+    raw = synth.random_hodbf(n=1024, dtype=capi.COMPLEX_F64, seed=9)
+    x = _x(np.random.default_rng(1), raw.num_cols, 1, True)
+    ys = []
+    for q in (1, 8, 1184):
+        t = Tables(raw, capi.OP_N, num_queues=q)
+        t.check_queues()
+        ys.append(t.apply(x))
+        t.close()
+    assert np.array_equal(ys[0], ys[1]) and np.array_equal(ys[0], ys[2])
+
+
+def test_oracle_transpose_is_adjoint():
+    """<A x, y> == <x, A^H y> for the oracle itself (independent sanity of the checker)."""
+    raw = synth.random_hodbf(n=700, dtype=capi.COMPLEX_F64, seed=2)
+    rng = np.random.default_rng(5)
+    x, y = _x(rng, 700, 1, True), _x(rng, 700, 1, True)
+    lhs = np.vdot(y, portlib.apply(raw, x, capi.OP_N))
+    rhs = np.vdot(portlib.apply(raw, y, capi.OP_H), x)
+    assert abs(lhs - rhs) / abs(lhs) < 1e-12
