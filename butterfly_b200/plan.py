@@ -130,7 +130,9 @@ class Plan:
         ldy = y.stride(0) if y.dim() == 2 else 1
         if x.shape[0] != self.rows_in(op) or y.shape[0] != self.rows_out(op):
             raise ValueError("shape mismatch")
-        s = C.c_void_p(stream) if stream else None
+        # NULL means "the plan's own stream" in the C ABI; torch's default stream has handle 0,
+        # which is the legacy default stream = cudaStreamLegacy (0x1) as an explicit handle
+        s = None if stream is None else C.c_void_p(stream if stream else 1)
         capi.check(
             self.lib.bfCudaApplyDevice(self.handle, op, C.c_void_p(x.data_ptr()), ldx, nrhs, C.c_void_p(y.data_ptr()), ldy, s),
             "bfCudaApplyDevice",
