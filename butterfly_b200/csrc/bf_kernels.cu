@@ -89,6 +89,37 @@ __device__ __forceinline__ unsigned char *rowPtr(const StageLaunch &a, uint32_t 
   return a.base[sp] + (long long)(addr & kRowMask) * a.ld[sp] * es;
 }
 
+// acc[p] += A[row(p), :] . x for every pass p of one staged tile.  NC = ceil(kc / G) register
+// chunks.  Lanes past the tile edge read a clamped (valid) element and multiply it by a zero
+// operand (column edge) or feed an accumulator nobody stores (row edge), so the loop body has no
+// predicates; passes are taken two at a time for ILP and left through a warp-uniform branch.
+template <bool CPLX, int NC, int P, int RPP, int G>
+__device__ __forceinline__ void tileFma(typename Scalar<CPLX>::T (&acc)[P], const typename Scalar<CPLX>::T *A,
+                                        const typename Scalar<CPLX>::T *xs, int rows, int kc, int g, int l) {
+  using S = Scalar<CPLX>;
+  using T = typename S::T;
+  T xr[NC];
+  int cj[NC];
+#pragma unroll
+  for (int tt = 0; tt < NC; ++tt) {
+    const int j = tt * G + l;
+    cj[tt] = min(j, kc - 1);
+    const T v = xs[cj[tt]];
+    xr[tt] = j < kc ? v : S::zero();
+  }
+#pragma unroll
+  for (int p = 0; p < P; p += 2) {
+    if (p * RPP >= rows) break;
+    const T *A0 = A + min(p * RPP + g, rows - 1) * kc;
+    const T *A1 = A + min((p + 1) * RPP + g, rows - 1) * kc;
+    T a0[NC], a1[NC];
+#pragma unroll
+    for (int tt = 0; tt < NC; ++tt) { a0[tt] = A0[cj[tt]]; a1[tt] = A1[cj[tt]]; }
+#pragma unroll
+    for (int tt = 0; tt < NC; ++tt) { S::fma(acc[p], a0[tt], xr[tt]); S::fma(acc[p + 1], a1[tt], xr[tt]); }
+  }
+}
+
 // ---- 1-RHS stage kernel ---------------------------------------------------------------------------
 template <bool CPLX>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid_constant__ StageLaunch a) {
@@ -190,27 +221,17 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       mbarWait(smemU32(&bars[slot]), (cSeq / kGemvSlots) & 1u);
 
       const T *xs = reinterpret_cast<const T *>(xsB);
-      T xr[KT];
-#pragma unroll
-      for (int tt = 0; tt < KT; ++tt) {
-        const int j = tt * G + l;
-        xr[tt] = (tt * G < kc && j < kc) ? xs[j] : S::zero();
-      }
       const T *A = reinterpret_cast<const T *>(As);
-#pragma unroll
-      for (int p = 0; p < P; ++p) {
-        if (p * RPP < rows) {
-          const int r = p * RPP + g;
-          const bool rv = r < rows;
-          const T *Ar = A + r * kc;
-#pragma unroll
-          for (int tt = 0; tt < KT; ++tt) {
-            if (tt * G < kc) {
-              const int j = tt * G + l;
-              if (rv && j < kc) S::fma(acc[p], Ar[j], xr[tt]);
-            }
-          }
-        }
+      // exact trip counts through real (warp-uniform) branches: no predicated-off FMA slots
+      switch ((kc + G - 1) / G) {
+      case 1: tileFma<CPLX, 1, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 2: tileFma<CPLX, 2, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 3: tileFma<CPLX, 3, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 4: tileFma<CPLX, 4, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 5: tileFma<CPLX, 5, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 6: tileFma<CPLX, 6, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 7: tileFma<CPLX, 7, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      default: tileFma<CPLX, 8, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
       }
       __syncwarp();
       produce(); // refill the slot just drained
