@@ -1,0 +1,173 @@
+"""ctypes wrapper of the UNMODIFIED reference library (oracle/_ref/libbutterfly_ref.so, compiled
+from /root/reference by oracle/Makefile) and of our thin C drivers around it
+(oracle/ref_driver.c).  TEST INFRASTRUCTURE, NOT PRODUCT: only tests/, smoke() and bench.py's
+cpu_baseline / --impl reference legs import this.  The prebuilt .so files travel to the GPU box;
+/root/reference itself is never read at run time.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from butterfly_b200 import capi
+from butterfly_b200.rawops import RawOps
+
+HERE = Path(__file__).resolve().parent
+REF_SO = HERE / "_ref" / "libbutterfly_ref.so"
+DRV_SO = HERE / "_ref" / "libbf_oracle_drv.so"
+
+_ref = _drv = _att = None
+
+
+def available() -> bool:
+    return REF_SO.exists() and DRV_SO.exists()
+
+
+def attach_available() -> bool:
+    return available() and capi.ATTACH_LIB_PATH.exists()
+
+
+def load():
+    global _ref, _drv
+    if _drv is None:
+        if not available():
+            raise FileNotFoundError("oracle/_ref is not built (run `make -C oracle ref` where /root/reference exists)")
+        _ref = C.CDLL(str(REF_SO), mode=C.RTLD_GLOBAL)
+        d = C.CDLL(str(DRV_SO), mode=C.RTLD_GLOBAL)
+        vp, i64, dbl = C.c_void_p, C.c_int64, C.c_double
+        d.refHelm2Build.argtypes = [vp, i64, dbl]; d.refHelm2Build.restype = vp
+        d.refHelm2GetMat.argtypes = [vp]; d.refHelm2GetMat.restype = vp
+        d.refHelm2GetPerm.argtypes = [vp, vp]; d.refHelm2GetPerm.restype = None
+        d.refHelm2DenseKernel.argtypes = [vp, vp]; d.refHelm2DenseKernel.restype = None
+        d.refHelm2Free.argtypes = [vp]; d.refHelm2Free.restype = None
+        d.refMatNumRows.argtypes = [vp]; d.refMatNumRows.restype = i64
+        d.refMatNumCols.argtypes = [vp]; d.refMatNumCols.restype = i64
+        d.refMatMulComplex.argtypes = [vp, vp, i64, i64, vp]; d.refMatMulComplex.restype = dbl
+        d.refMatMulVecReal.argtypes = [vp, vp, i64, vp, C.c_int]; d.refMatMulVecReal.restype = dbl
+        d.refPermuteRowsComplex.argtypes = [vp, i64, i64, vp]; d.refPermuteRowsComplex.restype = None
+        d.refReversePerm.argtypes = [vp, i64, vp]; d.refReversePerm.restype = None
+        d.refSeed.argtypes = [C.c_uint64]; d.refSeed.restype = None
+        d.refComplexRandn.argtypes = [i64, vp]; d.refComplexRandn.restype = None
+        d.refRealRandn.argtypes = [i64, vp]; d.refRealRandn.restype = None
+        d.refOpenblasThreads.argtypes = [C.c_int]; d.refOpenblasThreads.restype = C.c_int
+        d.refPrintBlocks.argtypes = [vp, C.c_char_p]; d.refPrintBlocks.restype = None
+        _drv = d
+    return _drv
+
+
+def load_attach():
+    """libbfcuda_attach.so: the C flattener + vtable attach, resolved against the loaded reference."""
+    global _att
+    if _att is None:
+        load()
+        capi.load_library()
+        a = C.CDLL(str(capi.ATTACH_LIB_PATH), mode=C.RTLD_GLOBAL)
+        a.bfCudaFlatten.argtypes = [C.c_void_p, C.POINTER(C.POINTER(capi.PlanDesc))]; a.bfCudaFlatten.restype = C.c_int32
+        a.bfCudaFlattenFree.argtypes = [C.POINTER(capi.PlanDesc)]; a.bfCudaFlattenFree.restype = None
+
+        class AttachOpts(C.Structure):
+            _fields_ = [("device", C.c_int32), ("buildTranspose", C.c_int32)]
+
+        a.AttachOpts = AttachOpts
+        a.bfCudaMatAttach.argtypes = [C.c_void_p, C.POINTER(AttachOpts)]; a.bfCudaMatAttach.restype = C.c_int32
+        a.bfCudaMatDetach.argtypes = [C.c_void_p]; a.bfCudaMatDetach.restype = C.c_int32
+        a.bfCudaMatGetPlan.argtypes = [C.c_void_p]; a.bfCudaMatGetPlan.restype = C.c_void_p
+        _att = a
+    return _att
+
+
+def circle_points(n: int) -> np.ndarray:
+    """examples/simple/make_circle_test_data.py:12-15"""
+    t = 2 * np.pi * np.arange(n) / n
+    return np.ascontiguousarray(np.stack([np.cos(t), np.sin(t)], axis=1))
+
+
+class Helm2:
+    """bfFacHelm2MakeMultilevel on a point set, as examples/simple/bf_all_blocks.c:96-130."""
+
+    def __init__(self, points: np.ndarray, k_wave: float):
+        self.drv = load()
+        pts = np.ascontiguousarray(points, dtype=np.float64)
+        self.n = len(pts)
+        self.h = self.drv.refHelm2Build(pts.ctypes.data, self.n, float(k_wave))
+        self.mat = self.drv.refHelm2GetMat(self.h)
+
+    def close(self):
+        if self.h:
+            self.drv.refHelm2Free(self.h)
+            self.h = None
+
+    def perm(self) -> np.ndarray:
+        p = np.zeros(self.n, np.int64)
+        self.drv.refHelm2GetPerm(self.h, p.ctypes.data)
+        return p
+
+    def dense_kernel(self) -> np.ndarray:
+        K = np.zeros((self.n, self.n), np.complex128)
+        self.drv.refHelm2DenseKernel(self.h, K.ctypes.data)
+        return K
+
+    def matmul(self, x: np.ndarray):
+        """bfMatMul(A, X) through the object's CURRENT vtable (reference CPU path, or the GPU path
+        once attached).  Returns (Y, seconds inside bfMatMul)."""
+        x = np.ascontiguousarray(x, dtype=np.complex128)
+        if x.ndim == 1:
+            x = x[:, None]
+        y = np.zeros((self.drv.refMatNumRows(self.mat), x.shape[1]), np.complex128)
+        t = self.drv.refMatMulComplex(self.mat, x.ctypes.data, x.shape[0], x.shape[1], y.ctypes.data)
+        return y, t
+
+    def flatten(self) -> RawOps:
+        a = load_attach()
+        d = C.POINTER(capi.PlanDesc)()
+        st = a.bfCudaFlatten(self.mat, C.byref(d))
+        if st != 0:
+            raise RuntimeError(f"bfCudaFlatten: status {st}")
+        try:
+            return RawOps.from_desc(d.contents)
+        finally:
+            a.bfCudaFlattenFree(d)
+
+    def attach(self, build_transpose=0):
+        a = load_attach()
+        o = a.AttachOpts(-1, build_transpose)
+        st = a.bfCudaMatAttach(self.mat, C.byref(o))
+        if st != 0:
+            raise capi.BfCudaError(st, "bfCudaMatAttach", capi.load_library().bfCudaLastErrorMessage().decode())
+
+    def detach(self):
+        st = load_attach().bfCudaMatDetach(self.mat)
+        if st != 0:
+            raise capi.BfCudaError(st, "bfCudaMatDetach")
+
+
+def randn_complex(n: int, seed: int = 0) -> np.ndarray:
+    """bfSeed(seed); bfComplexRandn(n) — the examples' RHS generator (src/rand.c:19-76)."""
+    d = load()
+    out = np.zeros(n, np.complex128)
+    d.refSeed(seed)
+    d.refComplexRandn(n, out.ctypes.data)
+    return out
+
+
+def permute_rows_complex(x: np.ndarray, perm: np.ndarray) -> np.ndarray:
+    """bfMatPermuteRows on a copy (src/mat_dense_complex.c:741-774)."""
+    d = load()
+    y = np.ascontiguousarray(x if x.ndim == 2 else x[:, None], dtype=np.complex128).copy()
+    p = np.ascontiguousarray(perm, dtype=np.int64)
+    d.refPermuteRowsComplex(y.ctypes.data, y.shape[0], y.shape[1], p.ctypes.data)
+    return y if x.ndim == 2 else y[:, 0]
+
+
+def reverse_perm(perm: np.ndarray) -> np.ndarray:
+    d = load()
+    p = np.ascontiguousarray(perm, dtype=np.int64)
+    r = np.zeros_like(p)
+    d.refReversePerm(p.ctypes.data, len(p), r.ctypes.data)
+    return r
+
+
+def set_blas_threads(n: int) -> int:
+    return load().refOpenblasThreads(n)

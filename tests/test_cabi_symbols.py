@@ -1,0 +1,48 @@
+"""CPU: the C-ABI library loads and exports every symbol include/*.h declares (no compute)."""
+import ctypes as C
+import re
+from pathlib import Path
+
+from butterfly_b200 import capi
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _declared(header):
+    txt = (ROOT / "include" / header).read_text()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(bfCuda[A-Za-z0-9]+)\s*\(", txt)))
+
+
+def test_libbfcuda_exports_everything_bf_cuda_h_declares(lib):
+    names = _declared("bf_cuda.h") + _declared("bf_cuda_debug.h")
+    assert len(names) >= 20
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    assert sorted(set(capi.EXPORTED_SYMBOLS + capi.DEBUG_EXPORTED_SYMBOLS)) == sorted(names)
+    assert lib.bfCudaAbiVersion() == capi.ABI_VERSION
+
+
+def test_attach_library_exports(lib):
+    import pytest
+
+    if not capi.ATTACH_LIB_PATH.exists():
+        pytest.skip("attach layer is only built where the reference headers exist")
+    out = __import__("subprocess").run(["nm", "-D", "--defined-only", str(capi.ATTACH_LIB_PATH)], capture_output=True, text=True).stdout
+    for n in _declared("bf_cuda_attach.h"):
+        assert f" T {n}" in out, n
+
+
+def test_no_device_fails_loudly(lib):
+    """On a machine without a GPU plan creation must fail with NO_DEVICE: there is no CPU fallback."""
+    import torch
+
+    if torch.cuda.is_available():
+        return
+    from butterfly_b200 import synth
+
+    raw = synth.random_rect(50, 40, capi.REAL_F64, seed=1)
+    d = raw.desc()
+    h = C.c_void_p()
+    assert lib.bfCudaPlanCreate(C.byref(d), C.byref(h)) == 5  # BF_CUDA_ERROR_NO_DEVICE
+    assert b"no CPU fallback" in lib.bfCudaLastErrorMessage()

@@ -1,0 +1,69 @@
+"""CPU: pin the oracle (oracle/plan_oracle.c) and the plan compiler against golden vectors that
+the UNMODIFIED reference produced (oracle/make_golden.py; bfMatMul, bfMatPermuteRows,
+bfPermGetReversePerm of the reference build).  Needs no reference at run time."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from butterfly_b200 import capi
+from butterfly_b200.rawops import RawOps
+from oracle import portlib
+from table_interp import Tables
+
+G = Path(__file__).resolve().parent / "golden"
+
+
+@pytest.fixture(scope="module")
+def block():
+    raw = RawOps.load(G / "helm2_block.npz")
+    io = np.load(G / "helm2_block_io.npz")
+    return raw, io["x"], io["y"]
+
+
+def test_port_oracle_reproduces_reference_bfmatmul(block):
+    raw, x, y = block
+    assert raw.dtype == capi.COMPLEX_F64 and raw.num_ops == 11 and raw.num_entries == 11184
+    yo = portlib.apply(raw, x)
+    assert np.linalg.norm(yo - y) / np.linalg.norm(y) < 1e-13
+
+
+def test_compiled_tables_reproduce_reference_bfmatmul(block):
+    raw, x, y = block
+    t = Tables(raw, capi.OP_N, 148 * 8)
+    try:
+        t.check_queues()
+        yt = t.apply(x)[:, 0]
+    finally:
+        t.close()
+    assert np.linalg.norm(yt - y) / np.linalg.norm(y) < 1e-13
+    assert t.num_stages == 3  # BlockDiag, BlockCoo, BlockDiag (src/fac_helm2.c:692-695)
+
+
+def test_permutations_bit_exact_with_reference():
+    m = np.load(G / "helm2_n2048_meta.npz")
+    perm, rev = m["perm"], m["rev_perm"]
+    # bfPermGetReversePerm (src/perm.c:195-220) is the inverse permutation
+    assert np.array_equal(np.argsort(perm), rev)
+    # out[perm[i]] = in[i] (src/mat_dense_complex.c:741-774)
+    assert np.array_equal(portlib.permute_rows(rev, m["x"]), m["x_permuted"])
+    assert np.array_equal(portlib.permute_rows(perm, m["y"]), m["y_permuted"])
+
+
+def test_raw_ops_file_roundtrip(block, lib, tmp_path):
+    import ctypes as C
+
+    raw, x, y = block
+    d = raw.desc()
+    path = str(tmp_path / "block.bfraw").encode()
+    assert lib.bfCudaRawOpsSave(C.byref(d), path) == 0
+    out = C.POINTER(capi.PlanDesc)()
+    assert lib.bfCudaRawOpsLoad(path, C.byref(out)) == 0
+    try:
+        back = RawOps.from_desc(out.contents)
+    finally:
+        lib.bfCudaRawOpsFree(out)
+    assert np.array_equal(back.fingerprint(), raw.fingerprint())
+    assert np.array_equal(back.buf_rows, raw.buf_rows)
+    assert np.array_equal(portlib.apply(back, x), portlib.apply(raw, x))
+    assert lib.bfCudaRawOpsLoad(str(tmp_path / "missing").encode(), C.byref(out)) == 6  # BF_CUDA_ERROR_IO

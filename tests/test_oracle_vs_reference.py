@@ -1,0 +1,64 @@
+"""CPU, only where oracle/_ref exists: the flattener + port oracle + plan tables against the
+reference's own bfMatMul on a live fac_helm2 factorization (the pin SURVEY.md §8c names:
+examples/simple/bf_all_blocks.c:136-153)."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from butterfly_b200 import capi
+from oracle import portlib, reflib
+from table_interp import Tables
+
+pytestmark = [
+    pytest.mark.reference,
+    pytest.mark.skipif(not (reflib.available() and capi.ATTACH_LIB_PATH.exists()), reason="oracle/_ref or the attach layer is not built"),
+]
+G = Path(__file__).resolve().parent / "golden"
+
+
+@pytest.fixture(scope="module")
+def helm():
+    h = reflib.Helm2(reflib.circle_points(2048), 50.0)
+    yield h
+    h.close()
+
+
+def test_flatten_matches_golden_structure(helm):
+    m = np.load(G / "helm2_n2048_meta.npz")
+    raw = helm.flatten()
+    assert np.array_equal(raw.fingerprint(), m["fingerprint"]), "flattened index tables changed"
+    assert np.array_equal(raw.buf_rows, m["buf_rows"])
+    assert raw.num_entries == int(m["num_entries"])
+    assert np.array_equal(helm.perm(), m["perm"])
+
+
+def test_reference_reproduces_its_golden_output(helm):
+    m = np.load(G / "helm2_n2048_meta.npz")
+    assert np.array_equal(reflib.randn_complex(2048, 0), m["x"])  # bfSeed(0) + bfComplexRandn
+    y, _ = helm.matmul(m["x"])
+    assert np.linalg.norm(y[:, 0] - m["y"]) / np.linalg.norm(m["y"]) < 1e-14
+
+
+@pytest.mark.parametrize("nrhs", [1, 3])
+def test_port_oracle_and_tables_match_reference(helm, nrhs):
+    m = np.load(G / "helm2_n2048_meta.npz")
+    x = m["x"][:, None] if nrhs == 1 else m["x3"]
+    y_ref, _ = helm.matmul(x)
+    raw = helm.flatten()
+    y_port = portlib.apply(raw, x)
+    assert np.linalg.norm(y_port - y_ref) / np.linalg.norm(y_ref) < 1e-13
+    t = Tables(raw, capi.OP_N, 148 * 8)
+    try:
+        y_tab = t.apply(x)
+    finally:
+        t.close()
+    assert np.linalg.norm(y_tab - y_ref) / np.linalg.norm(y_ref) < 1e-13
+
+
+def test_butterfly_vs_dense_kernel_pin(helm):
+    """The reference's own accuracy check (bf_all_blocks.c:149-153): butterfly vs dense kernel."""
+    x = reflib.randn_complex(2048, 0)
+    y, _ = helm.matmul(x)
+    yd = helm.dense_kernel() @ x
+    assert np.linalg.norm(y[:, 0] - yd) / np.linalg.norm(yd) < 1e-11
