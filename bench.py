@@ -1,0 +1,323 @@
+#!/usr/bin/env python
+"""bench.py — butterfly apply throughput on B200 (contract: see DESIGN.md §6).
+
+A step = one apply Y = A X of the flattened Helmholtz HODBF (reference fac_helm2 structure on N
+unit-circle points, synthetic values) to an n x nrhs complex-fp64 block.  `value` is whole-job
+GFLOP/s (flops = 8 E nrhs) with X, Y resident in HBM; `e2e` is the same metric
+through the host-buffer C-ABI call (bfCudaApplyHost: what the swapped bfMatMul vtable slot calls),
+H2D and D2H inside the timed region.  N > 1 GPUs: one process per GPU, plan replicated, the RHS
+columns sharded across ranks (no collective on the data path; weak scaling in RHS).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+DEFAULT_N = 524288  # largest rung of the ladder (2^20, 2^19, 2^18) whose factors fit 180 GB of HBM
+                    # at the example's 41 points per wavelength: 2^20 needs 186 GB
+CPU_SAMPLE_N = 8192
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=int(os.environ.get("BF_BENCH_N", DEFAULT_N)))
+    ap.add_argument("--k", type=float, default=0.0, help="wavenumber (default n / 40.96)")
+    ap.add_argument("--nrhs", type=int, default=1, help="RHS columns PER GPU")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self.stop, self.t = index, [], False, None
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([s.strip() for s in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        import statistics
+
+        mhz = [int(s[0]) for s in self.samples if s and s[0].isdigit()]
+        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith("active")})
+        return {"sm_mhz": int(statistics.median(mhz)) if mhz else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_reference_leg(steps, warmup, sample_n=CPU_SAMPLE_N):
+    """The reference's own CPU bfMatMul (oracle/_ref = unmodified sources + OpenBLAS) on a bounded
+    sample of the workload: the same generator at a smaller N, REAL factor values, 1 RHS."""
+    import numpy as np
+
+    from oracle import reflib
+
+    if not reflib.available():
+        # the oracle port on a synthetic operator of the same family
+        from butterfly_b200 import capi, synth
+        from oracle import portlib
+
+        raw = synth.random_hodbf(n=sample_n, dtype=capi.COMPLEX_F64, seed=1, leaf=64, rank_lo=16, rank_hi=40, exotic=False)
+        x = np.random.default_rng(0).standard_normal((sample_n, 1)) + 0j
+        ts = []
+        for i in range(warmup + steps):
+            t0 = time.perf_counter(); portlib.apply(raw, x); ts.append(time.perf_counter() - t0)
+        t = float(np.median(ts[warmup:]))
+        return {"value": 8 * raw.num_entries / t / 1e9, "unit": "GFLOP/s", "cores": 1, "kind": "port",
+                "sample": f"oracle port, synthetic HODBF n={sample_n}, 1 RHS, median of {steps}", "ms_per_step": t * 1e3, "entries": raw.num_entries}
+    k = sample_n / 40.96
+    t0 = time.perf_counter()
+    h = reflib.Helm2(reflib.circle_points(sample_n), k)
+    build_s = time.perf_counter() - t0
+    E = h.flatten().num_entries if reflib.attach_available() else None
+    x = reflib.randn_complex(sample_n, 0)
+    best = None
+    ncpu = os.cpu_count() or 1
+    for threads in sorted({1, ncpu}):
+        used = reflib.set_blas_threads(threads)
+        ts = [h.matmul(x)[1] for _ in range(warmup + steps)]
+        t = float(np.median(ts[warmup:]))
+        if best is None or t < best[0]:
+            best = (t, used)
+    h.close()
+    t, used = best
+    if E is None:
+        E = int(2112 * sample_n)
+    return {"value": 8 * E / t / 1e9, "unit": "GFLOP/s", "cores": int(used), "kind": "reference",
+            "sample": f"reference bfMatMul (unmodified sources, OpenBLAS) on fac_helm2 circle N={sample_n} k={k:g} (same generator, smaller N; built in {build_s:.1f}s), 1 RHS, median of {steps}, best of 1 and {ncpu} BLAS threads",
+            "ms_per_step": t * 1e3, "entries": int(E), "matvecs_per_s": 1.0 / t}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return  # rank 0 alone runs the CPU arm
+    r = cpu_reference_leg(args.steps, max(args.warmup, 1))
+    k = args.k or args.n / 40.96
+    line = {
+        "impl": "reference", "metric": "butterfly apply GFLOP/s (complex fp64, 1 RHS)", "value": r["value"], "unit": "GFLOP/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "c128 (complex f64)", "data": "synthetic",
+        "config": {"workload": f"helm2_circle N={args.n} k={k:g} nrhs=1 (timed on the bounded sample below)"},
+        "matvecs_per_s": r.get("matvecs_per_s"),
+        "cpu_baseline": {k2: r[k2] for k2 in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from butterfly_b200 import capi, workloads
+    from butterfly_b200.plan import Plan
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n, nrhs = args.n, args.nrhs
+    # structure: rank 0 of the node generates (cached on disk), the others wait and load it
+    if world > 1 and rank != 0:
+        dist.barrier()
+    raw, meta = workloads.helm2_circle(n, args.k or None)
+    if world > 1 and rank == 0:
+        dist.barrier()
+    t0 = time.time()
+    plan = Plan(raw, device=local_rank)
+    plan.fill_synthetic(2024)
+    info = plan.info
+    E = info["numEntries"]
+    build_s = time.time() - t0
+    stream = torch.cuda.current_stream().cuda_stream
+
+    g = torch.Generator(device="cuda").manual_seed(rank)
+    x = torch.randn(n, nrhs, dtype=torch.complex128, device="cuda", generator=g)
+    y = torch.empty(n, nrhs, dtype=torch.complex128, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        plan.apply_device(x, y, stream=stream)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        ev0.record()
+        for _ in range(args.steps):
+            plan.apply_device(x, y, stream=stream)
+        ev1.record()
+        barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = plan.last_launch_count * args.steps
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    total_rhs = nrhs * world
+    gflops = 8.0 * E * total_rhs / (ms_step * 1e-3) / 1e9
+
+    # per-stage times of one profiled apply (dominant kernel share, smallest/largest stage)
+    plan.set_profiling(True)
+    plan.apply_device(x, y, stream=stream)
+    torch.cuda.synchronize()
+    stage_ms = plan.stage_times_ms()
+    plan.set_profiling(False)
+    stage_entries = plan.stage_entries()
+
+    # end to end through the host-buffer C-ABI call, pinned host memory
+    xh = torch.randn(n, nrhs, dtype=torch.complex128).pin_memory()
+    yh = torch.empty(n, nrhs, dtype=torch.complex128).pin_memory()
+    xn, yn = xh.numpy(), yh.numpy()
+    for _ in range(2):
+        plan.apply_host(xn, capi.OP_N, out=yn)
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        plan.apply_host(xn, capi.OP_N, out=yn)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_gflops = 8.0 * E * total_rhs / e2e_s / 1e9
+    checksum = float(np.abs(yn).sum())
+
+    peak, peak_src = peaks()
+    alg_bytes = 16.0 * E + 16.0 * nrhs * (2 * n)  # per apply, per GPU
+    n_stage = max(len(stage_ms), 1)
+    achieved = alg_bytes / (ms_step * 1e-3) / 1e9
+    roof = {
+        "bound": "hbm" if nrhs < 16 else "fp64", "kernel": "bfGemvStage<complex>" if nrhs == 1 else "bfWideStage<complex>",
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+        "traffic": None,
+        "algorithmic_bytes_per_launch": alg_bytes / n_stage, "launches_per_step": int(plan.last_launch_count),
+        "avg_launch_ms": ms_step / n_stage,
+        "stage_ms": [round(float(v), 4) for v in stage_ms],
+        "stage_gbs": [round(16.0 * float(e) / max(float(m), 1e-9) / 1e6, 1) for e, m in zip(stage_entries, stage_ms)],
+    }
+    tr = ROOT / "profiles" / "traffic.json"
+    if tr.exists():
+        try:
+            roof["traffic"] = json.loads(tr.read_text()).get("gemv_bytes_per_launch")
+        except Exception:
+            pass
+
+    extra = None
+    if not args.no_extra and nrhs == 1 and world == 1:
+        # side measurement: the 256-RHS block apply on the same operator (configs[2])
+        try:
+            nr = 256
+            X = torch.randn(n, nr, dtype=torch.complex128, device="cuda")
+            Y = torch.empty(n, nr, dtype=torch.complex128, device="cuda")
+            plan.apply_device(X, Y, stream=stream)
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            reps = 2
+            for _ in range(reps):
+                plan.apply_device(X, Y, stream=stream)
+            a1.record()
+            torch.cuda.synchronize()
+            ms = a0.elapsed_time(a1) / reps
+            extra = {"nrhs": nr, "ms_per_apply": ms, "gflops": 8.0 * E * nr / (ms * 1e-3) / 1e9, "matvecs_per_s": nr / (ms * 1e-3)}
+            del X, Y
+        except Exception as e:  # e.g. out of memory for the workspace
+            extra = {"nrhs": 256, "error": str(e)[:200]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_reference_leg(steps=10, warmup=2)
+        cpu = {k2: cpu[k2] for k2 in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        k = args.k or n / 40.96
+        line = {
+            "metric": "butterfly apply GFLOP/s (complex fp64, 1 RHS)" if nrhs == 1 else f"butterfly apply GFLOP/s (complex fp64, {nrhs} RHS per GPU)",
+            "value": gflops, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "c128 (complex f64)", "data": "synthetic",
+            "config": {"workload": f"helm2_circle N={n} k={k:g} nrhs={nrhs}/GPU", "structure": meta["structure"],
+                       "E": int(E), "pool_GB": info["poolBytes"] / 1e9, "stages": int(info["numStagesN"]),
+                       "parallelism": f"rhs-columns x{world} (plan replicated, no collective)",
+                       "l2": "inputs larger than L2 (factor pool streamed once per apply)", "plan_build_s": round(build_s, 1)},
+            "matvecs_per_s": total_rhs / (ms_step * 1e-3),
+            "clocks": clk.summary(),
+            "e2e": {"value": e2e_gflops, "unit": "GFLOP/s", "h2d_bytes_per_step": int(16 * n * nrhs), "d2h_bytes_per_step": int(16 * n * nrhs),
+                    "ms_per_step": e2e_s * 1e3, "api": "bfCudaApplyHost (pinned host buffers)", "result_checksum": checksum},
+            "gpu_launches": int(launches),
+            "roofline": roof,
+            "cpu_baseline": cpu,
+            "rhs256": extra,
+        }
+        print(json.dumps(line), flush=True)
+    plan.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -78,13 +78,12 @@ class RawOps:
         buf_rows = np.ctypeslib.as_array(desc.bufRows, shape=(int(desc.numBufs),)).copy()
         cplx = desc.dtype == capi.COMPLEX_F64
         e = 2 if cplx else 1
-        sizes = np.zeros(n, np.int64)
-        for i in range(n):
-            o = ops[i]
-            if o["kind"] == capi.LEAF_DENSE:
-                sizes[i] = o["m"] * o["k"] * e
-            elif o["kind"] == capi.LEAF_DIAG:
-                sizes[i] = min(o["m"], o["k"])
+        sizes = np.where(ops["kind"] == capi.LEAF_DENSE, ops["m"] * ops["k"] * e,
+                         np.where(ops["kind"] == capi.LEAF_DIAG, np.minimum(ops["m"], ops["k"]), 0)).astype(np.int64) if n else np.zeros(0, np.int64)
+        if n and not ops["val"][sizes > 0].any():
+            # value-less descriptor (structure only): nothing to gather
+            ops["val"] = 0
+            return cls(desc.dtype, desc.numRows, desc.numCols, buf_rows, ops, None)
         offs = np.concatenate([[0], np.cumsum(sizes)])
         pool = np.zeros(int(offs[-1]), np.float64)
         for i in range(n):
