@@ -264,18 +264,21 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
 }
 
 // ---- many-RHS stage kernel ------------------------------------------------------------------------
-// Thread (rg, c): column c of the RHS chunk, rows rg, rg + NRG, ... of every item.  The A tile is a
-// warp-uniform LDS broadcast; the operand row X[j, :] is one coalesced global load per thread and is
-// reused for RT rows (4 DFMA each for complex), so the inner loop is fp64-pipe bound.
-template <bool CPLX, int NC>
-__global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_constant__ StageLaunch a) {
+// Register-blocked: a CTA of 4 warps owns an item (<= R rows) x (32 * CT) RHS columns.  Thread
+// (ty = warp, tx = lane) accumulates rows ty, ty + 4, ... against columns tx, tx + 32, ...: every A
+// element is one warp-uniform LDS broadcast reused for CT columns, every operand element one
+// coalesced global load reused for RT rows, i.e. 4 * RT * CT DFMA per (RT + CT) loads per k-step
+// for complex.  fp64-pipe bound; the A tiles arrive through the same TMA ring as in
+// the 1-RHS kernel, one ring per CTA.
+template <bool CPLX, int CT>
+__global__ void __launch_bounds__(kWideThreads) bfWideStage(const __grid_constant__ StageLaunch a) {
   using S = Scalar<CPLX>;
   using T = typename S::T;
   constexpr int ES = CPLX ? 16 : 8;
   constexpr int R = CPLX ? kMaxRowsComplex : kMaxRowsReal;
-  constexpr int NRG = kWideThreads / NC;
-  static_assert(NRG >= 1 && NRG <= R && R % NRG == 0, "row groups");
-  constexpr int RT = R / NRG;
+  constexpr int TY = kWideThreads / 32;
+  constexpr int RT = R / TY;
+  constexpr int NC = 32 * CT;
 
   extern __shared__ __align__(128) unsigned char smem[];
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kWideSlots * kTileBytes);
@@ -287,17 +290,19 @@ __global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_cons
   }
   __syncthreads();
 
-  const int q0 = blockIdx.x * kWarpsPerCta;
+  const int q0 = blockIdx.x * kWideQueuesPerCta;
   if (q0 >= a.numQueues) return;
-  const int q1 = min(q0 + kWarpsPerCta, a.numQueues);
+  const int q1 = min(q0 + kWideQueuesPerCta, a.numQueues);
   const uint32_t iBeg = a.qItemBegin[q0], iEnd = a.qItemBegin[q1];
   const uint32_t tEnd = a.qTileBegin[q1];
   if (iBeg == iEnd) return;
   const uint64_t pol = policyEvictFirst();
 
-  const int c = tid % NC, rg = tid / NC;
-  const long long col = (long long)a.colBegin + (long long)blockIdx.y * NC + c;
-  const bool colOk = col < a.nrhs;
+  const int tx = tid & 31, ty = tid >> 5;
+  const long long col0 = (long long)a.colBegin + (long long)blockIdx.y * NC + tx;
+  bool colOk[CT];
+#pragma unroll
+  for (int c = 0; c < CT; ++c) colOk[c] = col0 + 32 * c < a.nrhs;
 
   uint32_t pT = a.qTileBegin[q0], pSeq = 0, cSeq = 0;
   const unsigned char *pPool = a.pool + a.qPool16[q0] * 16ull;
@@ -327,9 +332,11 @@ __global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_cons
   for (uint32_t i = iBeg; i < iEnd; ++i) {
     const DevItem it = a.items[i];
     const int rows = it.rows;
-    T acc[RT];
+    T acc[RT][CT];
 #pragma unroll
-    for (int u = 0; u < RT; ++u) acc[u] = S::zero();
+    for (int u = 0; u < RT; ++u)
+#pragma unroll
+      for (int c = 0; c < CT; ++c) acc[u][c] = S::zero();
 
 #pragma unroll 1
     for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
@@ -337,13 +344,18 @@ __global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_cons
       const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
       const uint32_t sp = tl.inAddr >> 30;
       const long long ldIn = a.ld[sp];
-      const T *xp = reinterpret_cast<const T *>(a.base[sp]) + (long long)(tl.inAddr & kRowMask) * ldIn + col;
+      const T *xp = reinterpret_cast<const T *>(a.base[sp]) + (long long)(tl.inAddr & kRowMask) * ldIn + col0;
       if (tl.kc >= kKcDiag) {
         const double *dg = reinterpret_cast<const double *>(cPool);
 #pragma unroll
         for (int u = 0; u < RT; ++u) {
-          const int r = u * NRG + rg;
-          if (r < rows && colOk) S::fmaReal(acc[u], tl.kc == kKcDiag ? dg[r] : 1.0, xp[(long long)r * ldIn]);
+          const int r = u * TY + ty;
+          if (r < rows) {
+            const double d = tl.kc == kKcDiag ? dg[r] : 1.0;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+              if (colOk[c]) S::fmaReal(acc[u][c], d, xp[(long long)r * ldIn + 32 * c]);
+          }
         }
         cPool += bytes;
         continue;
@@ -351,54 +363,243 @@ __global__ void __launch_bounds__(kWideThreads, 1) bfWideStage(const __grid_cons
       const int kc = tl.kc;
       const uint32_t slot = cSeq % kWideSlots;
       const T *A = reinterpret_cast<const T *>(smem + slot * kTileBytes);
-      mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
 
-      int j = 0;
-#pragma unroll 1
-      for (; j + 4 <= kc; j += 4) {
-        T x0 = S::zero(), x1 = S::zero(), x2 = S::zero(), x3 = S::zero();
-        if (colOk) {
-          x0 = xp[(long long)(j + 0) * ldIn]; x1 = xp[(long long)(j + 1) * ldIn];
-          x2 = xp[(long long)(j + 2) * ldIn]; x3 = xp[(long long)(j + 3) * ldIn];
-        }
+      // the operand row of step j + 1 is fetched while step j computes
+      T xa[CT];
+#pragma unroll
+      for (int c = 0; c < CT; ++c) xa[c] = colOk[c] ? xp[32 * c] : S::zero();
+      mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
+      int ro[RT]; // row offsets into the tile; rows past the edge are clamped (never stored)
+#pragma unroll
+      for (int u = 0; u < RT; ++u) ro[u] = min(u * TY + ty, rows - 1) * kc;
+#pragma unroll 2
+      for (int j = 0; j < kc; ++j) {
+        T xn[CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) xn[c] = (colOk[c] && j + 1 < kc) ? xp[(long long)(j + 1) * ldIn + 32 * c] : S::zero();
 #pragma unroll
         for (int u = 0; u < RT; ++u) {
-          const int r = u * NRG + rg;
-          if (r < rows) {
-            const T *Ar = A + r * kc + j;
-            S::fma(acc[u], Ar[0], x0); S::fma(acc[u], Ar[1], x1);
-            S::fma(acc[u], Ar[2], x2); S::fma(acc[u], Ar[3], x3);
+          if (u * TY < rows) { // warp-uniform
+            const T av = A[ro[u] + j];
+#pragma unroll
+            for (int c = 0; c < CT; ++c) S::fma(acc[u][c], av, xa[c]);
           }
         }
-      }
-#pragma unroll 1
-      for (; j < kc; ++j) {
-        const T x0 = colOk ? xp[(long long)j * ldIn] : S::zero();
 #pragma unroll
-        for (int u = 0; u < RT; ++u) {
-          const int r = u * NRG + rg;
-          if (r < rows) S::fma(acc[u], A[r * kc + j], x0);
-        }
+        for (int c = 0; c < CT; ++c) xa[c] = xn[c];
       }
-      __syncthreads(); // every thread is done with this slot
+      __syncthreads(); // every warp is done with this slot
       produce();
       ++cSeq;
       cPool += bytes;
     }
 
-    if (colOk) {
+    const uint32_t sp = it.outAddr >> 30;
+    const long long ldOut = a.ld[sp];
+#pragma unroll
+    for (int u = 0; u < RT; ++u) {
+      const int r = u * TY + ty;
+      if (r < rows) {
+        long long row = (long long)(it.outAddr & kRowMask) + r;
+        if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
+        T *dst = reinterpret_cast<T *>(a.base[sp]) + row * ldOut + col0;
+#pragma unroll
+        for (int c = 0; c < CT; ++c) {
+          if (colOk[c]) {
+            T v = acc[u][c];
+            if (it.flags & kItemAccumulate) v = S::add(v, dst[32 * c]);
+            dst[32 * c] = v;
+          }
+        }
+      }
+    }
+  }
+}
+
+// ---- many-RHS stage kernel, complex: DMMA (fp64 tensor-core) contraction ---------------------------
+// With >= 2 RHS columns a stage is a batch of small dense contractions C(rows x nrhs) += A(rows x kc)
+// X(kc x nrhs).  One warp owns all <= 32 rows of the item x (8 * NB) RHS columns as MB x NB
+// m8n8k4 accumulator fragments, separately for the real and the imaginary part:
+//     Cr += Ar Xr + (-Ai) Xi        Ci += Ar Xi + Ai Xr          (4 DMMA per fragment per k-step)
+// A fragments are LDS.128 (re, im together) from the TMA-staged tile; X fragments are 16-byte global
+// loads (8 consecutive columns of a row = one 128-byte line per k) issued one k-step ahead of the
+// 16 * NB * MB DMMA that consume them, so their latency hides behind the tensor pipe.  Rows / k past
+// the tile edge use clamped (valid) addresses; k past the edge multiplies by a zeroed A fragment.
+__device__ __forceinline__ void dmma884(double (&c)[2], const double a, const double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+template <int NB>
+__global__ void __launch_bounds__(kWideThreads) bfWideMmaStage(const __grid_constant__ StageLaunch a) {
+  constexpr int ES = 16;
+  constexpr int MB = kMaxRowsComplex / 8;
+  constexpr int NC = (kWideThreads / 32) * NB * 8;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kWideSlots * kTileBytes);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kWideSlots; ++s) mbarInit(smemU32(&bars[s]), 1);
+    fenceBarrierInit();
+  }
+  __syncthreads();
+
+  const int q0 = blockIdx.x * kWideQueuesPerCta;
+  if (q0 >= a.numQueues) return;
+  const int q1 = min(q0 + kWideQueuesPerCta, a.numQueues);
+  const uint32_t iBeg = a.qItemBegin[q0], iEnd = a.qItemBegin[q1];
+  const uint32_t tEnd = a.qTileBegin[q1];
+  if (iBeg == iEnd) return;
+  const uint64_t pol = policyEvictFirst();
+
+  const int lane = tid & 31, g = lane >> 2, t4 = lane & 3;
+  const long long cw = (long long)a.colBegin + (long long)blockIdx.y * NC + (long long)(tid >> 5) * (NB * 8);
+  const bool active = cw < a.nrhs; // warp-uniform
+  long long cb[NB];                // column this lane supplies to the B fragment of block nb (clamped)
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) cb[nb] = min(cw + nb * 8 + g, (long long)a.nrhs - 1);
+
+  uint32_t pT = a.qTileBegin[q0], pSeq = 0, cSeq = 0;
+  const unsigned char *pPool = a.pool + a.qPool16[q0] * 16ull;
+  const unsigned char *cPool = pPool;
+  auto produce = [&]() {
+    while (pT < tEnd) {
+      const DevTile t = a.tiles[pT];
+      ++pT;
+      const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
+      const unsigned char *src = pPool;
+      pPool += bytes;
+      if (t.kc >= kKcDiag) continue;
+      if (tid == 0) {
+        const uint32_t slot = pSeq % kWideSlots;
+        const uint32_t bar = smemU32(&bars[slot]);
+        mbarExpectTx(bar, bytes);
+        bulkLoadHint(smemU32(smem + slot * kTileBytes), src, bytes, bar, pol);
+      }
+      ++pSeq;
+      return;
+    }
+  };
+#pragma unroll 1
+  for (int s = 0; s < kWideSlots; ++s) produce();
+
+#pragma unroll 1
+  for (uint32_t i = iBeg; i < iEnd; ++i) {
+    const DevItem it = a.items[i];
+    const int rows = it.rows;
+    double cr[MB][NB][2], ci[MB][NB][2];
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) { cr[mb][nb][0] = cr[mb][nb][1] = 0.0; ci[mb][nb][0] = ci[mb][nb][1] = 0.0; }
+
+#pragma unroll 1
+    for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
+      const DevTile tl = a.tiles[t];
+      const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
+      const uint32_t sp = tl.inAddr >> 30;
+      const long long ldIn = a.ld[sp];
+      const double2 *xrow = reinterpret_cast<const double2 *>(a.base[sp]) + (long long)(tl.inAddr & kRowMask) * ldIn;
+      if (tl.kc >= kKcDiag) {
+        if (active) {
+          const double *dg = reinterpret_cast<const double *>(cPool);
+#pragma unroll
+          for (int mb = 0; mb < MB; ++mb) {
+            const int r = mb * 8 + g;
+            if (r < rows) {
+              const double d = tl.kc == kKcDiag ? dg[r] : 1.0;
+#pragma unroll
+              for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                  const long long c = cw + nb * 8 + 2 * t4 + j;
+                  if (c < a.nrhs) {
+                    const double2 xv = xrow[(long long)r * ldIn + c];
+                    cr[mb][nb][j] = ::fma(d, xv.x, cr[mb][nb][j]);
+                    ci[mb][nb][j] = ::fma(d, xv.y, ci[mb][nb][j]);
+                  }
+                }
+            }
+          }
+        }
+        cPool += bytes;
+        continue;
+      }
+      const int kc = tl.kc;
+      const int ks = (kc + 3) >> 2;
+      const uint32_t slot = cSeq % kWideSlots;
+      const double2 *A = reinterpret_cast<const double2 *>(smem + slot * kTileBytes);
+
+      double2 xb[NB];
+      if (active) {
+        const long long k0 = min(t4, kc - 1);
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) xb[nb] = xrow[k0 * ldIn + cb[nb]];
+      }
+      mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
+      if (active) {
+        int ra[MB];
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) ra[mb] = min(mb * 8 + g, rows - 1) * kc;
+#pragma unroll 1
+        for (int s = 0; s < ks; ++s) {
+          double2 xn[NB];
+          if (s + 1 < ks) {
+            const long long k1 = min(s * 4 + 4 + t4, kc - 1);
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) xn[nb] = xrow[k1 * ldIn + cb[nb]];
+          }
+          const int k = s * 4 + t4;
+          const bool kOk = k < kc;
+          const int kcl = min(k, kc - 1);
+#pragma unroll
+          for (int mb = 0; mb < MB; ++mb) {
+            if (mb * 8 < rows) { // warp-uniform
+              double2 av = A[ra[mb] + kcl];
+              if (!kOk) av = make_double2(0.0, 0.0);
+              const double an = -av.y;
+#pragma unroll
+              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], av.x, xb[nb].x); dmma884(ci[mb][nb], av.x, xb[nb].y); }
+#pragma unroll
+              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], an, xb[nb].y); dmma884(ci[mb][nb], av.y, xb[nb].x); }
+            }
+          }
+          if (s + 1 < ks) {
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) xb[nb] = xn[nb];
+          }
+        }
+      }
+      __syncthreads(); // every warp is done with this slot
+      produce();
+      ++cSeq;
+      cPool += bytes;
+    }
+
+    if (active) {
       const uint32_t sp = it.outAddr >> 30;
       const long long ldOut = a.ld[sp];
+      const bool accum = (it.flags & kItemAccumulate) != 0;
 #pragma unroll
-      for (int u = 0; u < RT; ++u) {
-        const int r = u * NRG + rg;
+      for (int mb = 0; mb < MB; ++mb) {
+        const int r = mb * 8 + g;
         if (r < rows) {
           long long row = (long long)(it.outAddr & kRowMask) + r;
           if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
-          T *dst = reinterpret_cast<T *>(a.base[sp]) + row * ldOut + col;
-          T v = acc[u];
-          if (it.flags & kItemAccumulate) v = S::add(v, *dst);
-          *dst = v;
+          double2 *dst = reinterpret_cast<double2 *>(a.base[sp]) + row * ldOut;
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const long long c = cw + nb * 8 + 2 * t4 + j;
+              if (c < a.nrhs) {
+                double2 v = make_double2(cr[mb][nb][j], ci[mb][nb][j]);
+                if (accum) { const double2 o = dst[c]; v.x += o.x; v.y += o.y; }
+                dst[c] = v;
+              }
+            }
         }
       }
     }
@@ -487,11 +688,20 @@ cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int /*numSMs*/, cud
   return cudaGetLastError();
 }
 
-template <bool CPLX, int NC>
+template <bool CPLX, int CT>
 static cudaError_t launchWideT(const StageLaunch &a, int ncols, cudaStream_t stream) {
-  const int ctas = (a.numQueues + kWarpsPerCta - 1) / kWarpsPerCta;
+  const int ctas = (a.numQueues + kWideQueuesPerCta - 1) / kWideQueuesPerCta;
+  dim3 grid((unsigned)ctas, (unsigned)((ncols + 32 * CT - 1) / (32 * CT)));
+  bfWideStage<CPLX, CT><<<grid, kWideThreads, kWideSmemBytes, stream>>>(a);
+  return cudaGetLastError();
+}
+
+template <int NB>
+static cudaError_t launchWideMmaT(const StageLaunch &a, int ncols, cudaStream_t stream) {
+  constexpr int NC = (kWideThreads / 32) * NB * 8;
+  const int ctas = (a.numQueues + kWideQueuesPerCta - 1) / kWideQueuesPerCta;
   dim3 grid((unsigned)ctas, (unsigned)((ncols + NC - 1) / NC));
-  bfWideStage<CPLX, NC><<<grid, kWideThreads, kWideSmemBytes, stream>>>(a);
+  bfWideMmaStage<NB><<<grid, kWideThreads, kWideSmemBytes, stream>>>(a);
   return cudaGetLastError();
 }
 
@@ -499,16 +709,13 @@ cudaError_t launchWideStage(int dtype, const StageLaunch &a, int /*numSMs*/, cud
   const int ncols = a.nrhs - a.colBegin;
   if (ncols <= 0 || a.numQueues == 0) return cudaSuccess;
   if (dtype == BF_CUDA_COMPLEX_F64) {
-    if (ncols > 128) return launchWideT<true, 256>(a, ncols, stream);
-    if (ncols > 64) return launchWideT<true, 128>(a, ncols, stream);
-    if (ncols > 32) return launchWideT<true, 64>(a, ncols, stream);
-    if (ncols > 16) return launchWideT<true, 32>(a, ncols, stream);
-    return launchWideT<true, 16>(a, ncols, stream);
+    if (ncols > 64) return launchWideMmaT<4>(a, ncols, stream);
+    if (ncols > 32) return launchWideMmaT<2>(a, ncols, stream);
+    return launchWideMmaT<1>(a, ncols, stream);
   }
-  if (ncols > 128) return launchWideT<false, 256>(a, ncols, stream);
-  if (ncols > 64) return launchWideT<false, 128>(a, ncols, stream);
-  if (ncols > 32) return launchWideT<false, 64>(a, ncols, stream);
-  return launchWideT<false, 32>(a, ncols, stream);
+  if (ncols > 64) return launchWideT<false, 4>(a, ncols, stream);
+  if (ncols > 32) return launchWideT<false, 2>(a, ncols, stream);
+  return launchWideT<false, 1>(a, ncols, stream);
 }
 
 } // namespace bfc

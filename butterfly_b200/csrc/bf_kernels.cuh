@@ -30,9 +30,10 @@ constexpr int kGemvXBytes = 1056;                        // x segment: 64 c128 /
 constexpr int kGemvSlotBytes = kTileBytes + kGemvXBytes; // 9248
 constexpr int kGemvSmemBytes = kWarpsPerCta * kGemvSlots * (kGemvSlotBytes + 8) + 128;
 
-// Wide (many-RHS) kernel: CTA-wide ring of A tiles; one CTA owns kWarpsPerCta consecutive queues.
+// Wide (many-RHS) kernel: CTA-wide ring of A tiles; one CTA owns kWideQueuesPerCta consecutive queues.
 constexpr int kWideSlots = 4;
-constexpr int kWideThreads = 512;
+constexpr int kWideThreads = 128;       // 4 warps: warp = row group, lane = column group
+constexpr int kWideQueuesPerCta = 2;
 constexpr int kWideSmemBytes = kWideSlots * (kTileBytes + 8) + 128;
 
 // 1 RHS: y = A x, one warp per queue, TMA-staged tiles, shuffle reductions.
