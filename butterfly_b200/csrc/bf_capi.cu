@@ -300,6 +300,9 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
   if (nrhs < 0 || (nrhs > 0 && (ldx < nrhs || ldy < nrhs))) return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "ldx / ldy smaller than nrhs");
   if (nrhs == 0) { P->lastLaunches = 0; return BF_CUDA_OK; }
   if (!d_x || !d_y) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null operand");
+  if (reinterpret_cast<uintptr_t>(d_y) & (P->dtype == BF_CUDA_COMPLEX_F64 ? 15 : 7))
+    return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "d_y must be aligned to its element size");
+  if (reinterpret_cast<uintptr_t>(d_x) & 7) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "d_x must be 8-byte aligned");
   DeviceGuard g(P->device);
   DevDirection &dd = P->dir[op];
   const Direction &D = dd.host;
@@ -340,7 +343,7 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
     a.numQueues = D.numQueues; a.nrhs = (int)nc; a.colBegin = 0;
     // The 1-RHS kernel bulk-copies operand segments: they must be dense and 16-byte aligned (real
     // segments may start 8 bytes into a 16-byte window, so they always go through the padded copy).
-    const bool needStage = scatterIn != nullptr || (nc == 1 && (!cplx || ldx != 1 || (reinterpret_cast<uintptr_t>(xp) & 15)));
+    const bool needStage = scatterIn != nullptr || (cplx && (reinterpret_cast<uintptr_t>(xp) & 15)) || (nc == 1 && (!cplx || ldx != 1));
     if (needStage) {
       unsigned char *xs = P->scratch + wsBytes;
       cudaError_t e = launchPermuteRows(reinterpret_cast<const double *>(xp), ldx, reinterpret_cast<double *>(xs), nc,

@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   constexpr int P = 8;             // passes: RPP * P == max item rows
   constexpr int KT = 8;            // register chunks of G columns: G * KT == max tile columns
   static_assert(RPP * P == (CPLX ? kMaxRowsComplex : kMaxRowsReal), "item rows");
-  static_assert(G * KT == (CPLX ? kMaxKcComplex : kMaxKcReal), "tile columns");
+  static_assert(G * KT >= (CPLX ? kMaxKcComplex : kMaxKcReal), "tile columns");
   static_assert((CPLX ? kMaxKcComplex * 16 : kMaxKcReal * 8 + 16) <= kGemvXBytes, "x slot");
 
   extern __shared__ __align__(128) unsigned char smem[];
@@ -418,30 +418,57 @@ __global__ void __launch_bounds__(kWideThreads) bfWideStage(const __grid_constan
 
 // ---- many-RHS stage kernel, complex: DMMA (fp64 tensor-core) contraction ---------------------------
 // With >= 2 RHS columns a stage is a batch of small dense contractions C(rows x nrhs) += A(rows x kc)
-// X(kc x nrhs).  One warp owns all <= 32 rows of the item x (8 * NB) RHS columns as MB x NB
-// m8n8k4 accumulator fragments, separately for the real and the imaginary part:
-//     Cr += Ar Xr + (-Ai) Xi        Ci += Ar Xi + Ai Xr          (4 DMMA per fragment per k-step)
-// A fragments are LDS.128 (re, im together) from the TMA-staged tile; X fragments are 16-byte global
-// loads (8 consecutive columns of a row = one 128-byte line per k) issued one k-step ahead of the
-// 16 * NB * MB DMMA that consume them, so their latency hides behind the tensor pipe.  Rows / k past
-// the tile edge use clamped (valid) addresses; k past the edge multiplies by a zeroed A fragment.
+// X(kc x nrhs).  A CTA owns kWideQueuesPerCta queues x NC = 32 * NB RHS columns and is warp-specialised:
+//
+//   producer warp   walks the item / tile tables (the only global-memory reads of tables), allocates
+//                   each tile a span of ONE byte ring in shared memory — packed A values followed by
+//                   kc operand-row segments of NC columns (row stride padded by 32 bytes so that the
+//                   B-fragment LDS.128 is conflict-free) — issues the TMA bulk copies for both, and
+//                   publishes a 16-byte work entry {ring offset, shape, addresses, flags} under the
+//                   same "full" mbarrier the copies complete on.  It runs up to kMmaBars tiles
+//                   (~4 on average, several microseconds of DMMA work) ahead, which is what hides the
+//                   DRAM latency of the operand rows: X does not fit in L2 at 256 RHS.
+//   4 consumer warps  wait on "full", read the entry from shared memory, and own all <= 32 rows x the
+//                   8 * NB columns [w * 8 NB, ...) as MB x NB m8n8k4 accumulator fragments, separately
+//                   for the real and the imaginary part:
+//                       Cr += Ar Xr + (-Ai) Xi        Ci += Ar Xi + Ai Xr     (4 DMMA / fragment / k4)
+//                   then arrive on "empty" (which frees the ring span) and, after an item's last tile,
+//                   store it.  No CTA-wide barrier and no global load sits between two tiles.
+//
+// Rows / k past the tile edge use clamped (valid) addresses; k past the edge multiplies by a zeroed A
+// fragment; columns past nrhs are computed on stale shared memory and never stored.
 __device__ __forceinline__ void dmma884(double (&c)[2], const double a, const double b) {
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
       : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
+__device__ __forceinline__ void mbarArrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// work entry flags (word 0, above the 20-bit ring offset)
+constexpr uint32_t kEntFirst = 1u << 31, kEntLast = 1u << 30, kEntAccum = 1u << 29, kEntEnd = 1u << 28;
+constexpr uint32_t kEntOffMask = (1u << 20) - 1;
 
 template <int NB>
-__global__ void __launch_bounds__(kWideThreads) bfWideMmaStage(const __grid_constant__ StageLaunch a) {
+__global__ void __launch_bounds__(kMmaThreads) bfWideMmaStage(const __grid_constant__ StageLaunch a) {
   constexpr int ES = 16;
   constexpr int MB = kMaxRowsComplex / 8;
-  constexpr int NC = (kWideThreads / 32) * NB * 8;
+  constexpr int CW = kMmaThreads / 32 - 1; // consumer warps
+  constexpr int NC = CW * NB * 8;
+  constexpr uint32_t XS = NC * ES + 32;    // operand row stride in the ring
+  constexpr uint32_t RING = kMmaRingBytes;
+  // skip < size whenever the producer wraps, so 2 * size <= RING rules out a stall with nothing in flight
+  static_assert(2 * (kTileBytes + kMaxKcComplex * XS) <= RING, "largest tile must fit the ring twice");
+  static_assert(kMmaBars <= 32, "one lane per slot keeps its allocation size");
 
   extern __shared__ __align__(128) unsigned char smem[];
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kWideSlots * kTileBytes);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + RING);
+  uint64_t *empty = full + kMmaBars;
+  uint4 *entries = reinterpret_cast<uint4 *>(empty + kMmaBars);
   const int tid = threadIdx.x;
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < kWideSlots; ++s) mbarInit(smemU32(&bars[s]), 1);
+    for (int s = 0; s < kMmaBars; ++s) { mbarInit(smemU32(&full[s]), 1); mbarInit(smemU32(&empty[s]), CW); }
     fenceBarrierInit();
   }
   __syncthreads();
@@ -450,143 +477,167 @@ __global__ void __launch_bounds__(kWideThreads) bfWideMmaStage(const __grid_cons
   if (q0 >= a.numQueues) return;
   const int q1 = min(q0 + kWideQueuesPerCta, a.numQueues);
   const uint32_t iBeg = a.qItemBegin[q0], iEnd = a.qItemBegin[q1];
-  const uint32_t tEnd = a.qTileBegin[q1];
   if (iBeg == iEnd) return;
-  const uint64_t pol = policyEvictFirst();
 
-  const int lane = tid & 31, g = lane >> 2, t4 = lane & 3;
-  const long long cw = (long long)a.colBegin + (long long)blockIdx.y * NC + (long long)(tid >> 5) * (NB * 8);
-  const bool active = cw < a.nrhs; // warp-uniform
-  long long cb[NB];                // column this lane supplies to the B fragment of block nb (clamped)
-#pragma unroll
-  for (int nb = 0; nb < NB; ++nb) cb[nb] = min(cw + nb * 8 + g, (long long)a.nrhs - 1);
+  const int lane = tid & 31, warp = tid >> 5;
+  const long long c0 = (long long)a.colBegin + (long long)blockIdx.y * NC; // first column of the CTA
 
-  uint32_t pT = a.qTileBegin[q0], pSeq = 0, cSeq = 0;
-  const unsigned char *pPool = a.pool + a.qPool16[q0] * 16ull;
-  const unsigned char *cPool = pPool;
-  auto produce = [&]() {
-    while (pT < tEnd) {
-      const DevTile t = a.tiles[pT];
-      ++pT;
-      const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
-      const unsigned char *src = pPool;
-      pPool += bytes;
-      if (t.kc >= kKcDiag) continue;
-      if (tid == 0) {
-        const uint32_t slot = pSeq % kWideSlots;
-        const uint32_t bar = smemU32(&bars[slot]);
-        mbarExpectTx(bar, bytes);
-        bulkLoadHint(smemU32(smem + slot * kTileBytes), src, bytes, bar, pol);
+  if (warp == CW) {
+    // ===== producer =====
+    const uint64_t pol = policyEvictFirst();
+    const uint32_t rowBytes = (uint32_t)min((long long)NC, (long long)a.nrhs - c0) * ES;
+    const uint32_t ringBase = smemU32(smem);
+    const unsigned char *pPool = a.pool + a.qPool16[q0] * 16ull;
+    uint32_t pSeq = 0, oldest = 0, pOff = 0, inflight = 0;
+    uint32_t allocReg = 0; // lane s: bytes to free when slot s drains
+    // claim a slot and `size` contiguous ring bytes; returns the ring offset
+    auto claim = [&](uint32_t size) -> uint32_t {
+      const bool wrap = pOff + size > RING;
+      const uint32_t skip = wrap ? RING - pOff : 0u;
+      while (oldest + kMmaBars <= pSeq || inflight + skip + size > RING) {
+        const uint32_t os = oldest % kMmaBars;
+        mbarWait(smemU32(&empty[os]), (oldest / kMmaBars) & 1u);
+        inflight -= __shfl_sync(0xffffffffu, allocReg, os);
+        ++oldest;
       }
+      const uint32_t start = wrap ? 0u : pOff;
+      if (lane == (int)(pSeq % kMmaBars)) allocReg = skip + size;
+      pOff = start + size;
+      inflight += skip + size;
+      return start;
+    };
+    auto publish = [&](uint4 e, uint32_t txBytes) {
+      const uint32_t slot = pSeq % kMmaBars;
+      if (lane == 0) {
+        entries[slot] = e;
+        mbarExpectTx(smemU32(&full[slot]), txBytes); // release: the entry is visible to whoever sees the phase
+      }
+      __syncwarp();
       ++pSeq;
-      return;
-    }
-  };
+    };
 #pragma unroll 1
-  for (int s = 0; s < kWideSlots; ++s) produce();
-
-#pragma unroll 1
-  for (uint32_t i = iBeg; i < iEnd; ++i) {
-    const DevItem it = a.items[i];
-    const int rows = it.rows;
-    double cr[MB][NB][2], ci[MB][NB][2];
-#pragma unroll
-    for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-      for (int nb = 0; nb < NB; ++nb) { cr[mb][nb][0] = cr[mb][nb][1] = 0.0; ci[mb][nb][0] = ci[mb][nb][1] = 0.0; }
-
-#pragma unroll 1
-    for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
-      const DevTile tl = a.tiles[t];
-      const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
-      const uint32_t sp = tl.inAddr >> 30;
-      const long long ldIn = a.ld[sp];
-      const double2 *xrow = reinterpret_cast<const double2 *>(a.base[sp]) + (long long)(tl.inAddr & kRowMask) * ldIn;
-      if (tl.kc >= kKcDiag) {
-        if (active) {
-          const double *dg = reinterpret_cast<const double *>(cPool);
-#pragma unroll
-          for (int mb = 0; mb < MB; ++mb) {
-            const int r = mb * 8 + g;
-            if (r < rows) {
-              const double d = tl.kc == kKcDiag ? dg[r] : 1.0;
-#pragma unroll
-              for (int nb = 0; nb < NB; ++nb)
-#pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                  const long long c = cw + nb * 8 + 2 * t4 + j;
-                  if (c < a.nrhs) {
-                    const double2 xv = xrow[(long long)r * ldIn + c];
-                    cr[mb][nb][j] = ::fma(d, xv.x, cr[mb][nb][j]);
-                    ci[mb][nb][j] = ::fma(d, xv.y, ci[mb][nb][j]);
-                  }
-                }
-            }
-          }
-        }
-        cPool += bytes;
+    for (uint32_t i = iBeg; i < iEnd; ++i) {
+      const DevItem it = a.items[i];
+      const uint32_t accum = (it.flags & kItemAccumulate) ? kEntAccum : 0u;
+      if (it.numTiles == 0) {
+        claim(0);
+        publish(make_uint4(kEntFirst | kEntLast | accum, (uint32_t)it.rows << 16, 0u, it.outAddr), 0u);
         continue;
       }
-      const int kc = tl.kc;
-      const int ks = (kc + 3) >> 2;
-      const uint32_t slot = cSeq % kWideSlots;
-      const double2 *A = reinterpret_cast<const double2 *>(smem + slot * kTileBytes);
-
-      double2 xb[NB];
-      if (active) {
-        const long long k0 = min(t4, kc - 1);
-#pragma unroll
-        for (int nb = 0; nb < NB; ++nb) xb[nb] = xrow[k0 * ldIn + cb[nb]];
+#pragma unroll 1
+      for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
+        const DevTile tl = a.tiles[t];
+        const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
+        const uint32_t kEff = tl.kc >= kKcDiag ? tl.rows : tl.kc; // operand rows staged
+        const uint32_t start = claim(bytes + kEff * XS);
+        const uint32_t slot = pSeq % kMmaBars;
+        const uint32_t bar = smemU32(&full[slot]);
+        uint32_t w0 = start | accum;
+        if (t == it.tileBegin) w0 |= kEntFirst;
+        if (t + 1 == it.tileBegin + it.numTiles) w0 |= kEntLast;
+        publish(make_uint4(w0, (uint32_t)tl.kc | ((uint32_t)tl.rows << 16), bytes, it.outAddr), bytes + kEff * rowBytes);
+        if (lane == 0 && bytes) bulkLoadHint(ringBase + start, pPool, bytes, bar, pol);
+        const uint32_t sp = tl.inAddr >> 30;
+        const unsigned char *xsrc = a.base[sp] + ((long long)(tl.inAddr & kRowMask) * a.ld[sp] + c0) * ES;
+        for (uint32_t r = lane; r < kEff; r += 32)
+          bulkLoad(ringBase + start + bytes + r * XS, xsrc + (long long)r * a.ld[sp] * ES, rowBytes, bar);
+        pPool += bytes;
       }
-      mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
-      if (active) {
+    }
+    claim(0);
+    publish(make_uint4(kEntEnd, 0u, 0u, 0u), 0u);
+    return;
+  }
+
+  // ===== consumers =====
+  const int g = lane >> 2, t4 = lane & 3;
+  const long long cw = c0 + warp * (NB * 8); // first column of the warp
+  const bool active = cw < a.nrhs;           // warp-uniform
+  double cr[MB][NB][2], ci[MB][NB][2];
+#pragma unroll 1
+  for (uint32_t cSeq = 0;; ++cSeq) {
+    const uint32_t slot = cSeq % kMmaBars;
+    mbarWait(smemU32(&full[slot]), (cSeq / kMmaBars) & 1u);
+    const uint4 e = entries[slot];
+    if (e.x & kEntEnd) break;
+    const int rows = (int)(e.y >> 16);
+    const uint32_t kcRaw = e.y & 0xFFFFu;
+    if (e.x & kEntFirst) {
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) { cr[mb][nb][0] = cr[mb][nb][1] = 0.0; ci[mb][nb][0] = ci[mb][nb][1] = 0.0; }
+    }
+    if (active && kcRaw != 0) { // kc == 0: an item no leaf covers (stores zeros)
+      const unsigned char *T = smem + (e.x & kEntOffMask);
+      const unsigned char *Xw = T + e.z + (uint32_t)(warp * (NB * 8)) * ES; // the warp's operand columns
+      if (kcRaw >= kKcDiag) {
+        // y[r] += d[r] * x[r]: operand row r sits at ring row r
+        const double *dg = reinterpret_cast<const double *>(T);
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) {
+          const int r = mb * 8 + g;
+          if (r < rows) {
+            const double d = kcRaw == kKcDiag ? dg[r] : 1.0;
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                const double2 xv = *reinterpret_cast<const double2 *>(Xw + (uint32_t)r * XS + (nb * 8 + 2 * t4 + j) * ES);
+                cr[mb][nb][j] = ::fma(d, xv.x, cr[mb][nb][j]);
+                ci[mb][nb][j] = ::fma(d, xv.y, ci[mb][nb][j]);
+              }
+          }
+        }
+      } else {
+        const int kc = (int)kcRaw;
+        const int ks = (kc + 3) >> 2;
+        const double2 *A = reinterpret_cast<const double2 *>(T);
+        const unsigned char *Xs = Xw + g * ES;
         int ra[MB];
 #pragma unroll
         for (int mb = 0; mb < MB; ++mb) ra[mb] = min(mb * 8 + g, rows - 1) * kc;
-#pragma unroll 1
+        const int nmb = (rows + 7) >> 3;
+#pragma unroll 2
         for (int s = 0; s < ks; ++s) {
-          double2 xn[NB];
-          if (s + 1 < ks) {
-            const long long k1 = min(s * 4 + 4 + t4, kc - 1);
-#pragma unroll
-            for (int nb = 0; nb < NB; ++nb) xn[nb] = xrow[k1 * ldIn + cb[nb]];
-          }
           const int k = s * 4 + t4;
           const bool kOk = k < kc;
           const int kcl = min(k, kc - 1);
+          double2 xb[NB], av[MB];
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb) xb[nb] = *reinterpret_cast<const double2 *>(Xs + (uint32_t)kcl * XS + nb * (8 * ES));
 #pragma unroll
           for (int mb = 0; mb < MB; ++mb) {
-            if (mb * 8 < rows) { // warp-uniform
-              double2 av = A[ra[mb] + kcl];
-              if (!kOk) av = make_double2(0.0, 0.0);
-              const double an = -av.y;
+            av[mb] = A[ra[mb] + kcl];
+            if (!kOk) av[mb] = make_double2(0.0, 0.0);
+          }
 #pragma unroll
-              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], av.x, xb[nb].x); dmma884(ci[mb][nb], av.x, xb[nb].y); }
+          for (int mb = 0; mb < MB; ++mb)
+            if (mb < nmb) { // warp-uniform
 #pragma unroll
-              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], an, xb[nb].y); dmma884(ci[mb][nb], av.y, xb[nb].x); }
+              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], av[mb].x, xb[nb].x); dmma884(ci[mb][nb], av[mb].x, xb[nb].y); }
             }
-          }
-          if (s + 1 < ks) {
 #pragma unroll
-            for (int nb = 0; nb < NB; ++nb) xb[nb] = xn[nb];
-          }
+          for (int mb = 0; mb < MB; ++mb)
+            if (mb < nmb) {
+#pragma unroll
+              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], -av[mb].y, xb[nb].y); dmma884(ci[mb][nb], av[mb].y, xb[nb].x); }
+            }
         }
       }
-      __syncthreads(); // every warp is done with this slot
-      produce();
-      ++cSeq;
-      cPool += bytes;
     }
+    __syncwarp();
+    if (lane == 0) mbarArrive(smemU32(&empty[slot])); // the ring span and the entry may be reused
 
-    if (active) {
-      const uint32_t sp = it.outAddr >> 30;
+    if ((e.x & kEntLast) && active) {
+      const uint32_t sp = e.w >> 30;
       const long long ldOut = a.ld[sp];
-      const bool accum = (it.flags & kItemAccumulate) != 0;
+      const bool accum = (e.x & kEntAccum) != 0;
 #pragma unroll
       for (int mb = 0; mb < MB; ++mb) {
         const int r = mb * 8 + g;
         if (r < rows) {
-          long long row = (long long)(it.outAddr & kRowMask) + r;
+          long long row = (long long)(e.w & kRowMask) + r;
           if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
           double2 *dst = reinterpret_cast<double2 *>(a.base[sp]) + row * ldOut;
 #pragma unroll
@@ -677,6 +728,10 @@ cudaError_t configureKernels() {
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(bfGemvStage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfWideMmaStage<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfWideMmaStage<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaSmemBytes);
+  if (e != cudaSuccess) return e;
   return cudaSuccess;
 }
 
@@ -698,10 +753,10 @@ static cudaError_t launchWideT(const StageLaunch &a, int ncols, cudaStream_t str
 
 template <int NB>
 static cudaError_t launchWideMmaT(const StageLaunch &a, int ncols, cudaStream_t stream) {
-  constexpr int NC = (kWideThreads / 32) * NB * 8;
+  constexpr int NC = (kMmaThreads / 32 - 1) * NB * 8;
   const int ctas = (a.numQueues + kWideQueuesPerCta - 1) / kWideQueuesPerCta;
   dim3 grid((unsigned)ctas, (unsigned)((ncols + NC - 1) / NC));
-  bfWideMmaStage<NB><<<grid, kWideThreads, kWideSmemBytes, stream>>>(a);
+  bfWideMmaStage<NB><<<grid, kMmaThreads, kMmaSmemBytes, stream>>>(a);
   return cudaGetLastError();
 }
 
@@ -709,7 +764,6 @@ cudaError_t launchWideStage(int dtype, const StageLaunch &a, int /*numSMs*/, cud
   const int ncols = a.nrhs - a.colBegin;
   if (ncols <= 0 || a.numQueues == 0) return cudaSuccess;
   if (dtype == BF_CUDA_COMPLEX_F64) {
-    if (ncols > 64) return launchWideMmaT<4>(a, ncols, stream);
     if (ncols > 32) return launchWideMmaT<2>(a, ncols, stream);
     return launchWideMmaT<1>(a, ncols, stream);
   }

@@ -35,6 +35,11 @@ constexpr int kWideSlots = 4;
 constexpr int kWideThreads = 128;       // 4 warps: warp = row group, lane = column group
 constexpr int kWideQueuesPerCta = 2;
 constexpr int kWideSmemBytes = kWideSlots * (kTileBytes + 8) + 128;
+// DMMA (complex many-RHS) kernel: one byte ring per CTA holding A tiles + operand row segments.
+constexpr int kMmaThreads = 160;                  // 4 consumer warps + 1 producer warp
+constexpr int kMmaBars = 8;                       // tiles in flight
+constexpr int kMmaRingBytes = 96 * 1024;          // 2 CTAs / SM
+constexpr int kMmaSmemBytes = kMmaRingBytes + kMmaBars * (8 + 8 + 16) + 64;
 
 // 1 RHS: y = A x, one warp per queue, TMA-staged tiles, shuffle reductions.
 cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);

@@ -242,7 +242,9 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     const bool zeroOnly = frags[f].seq < 0;
     const int64_t nChunks = (el.len + R - 1) / R;
     for (int64_t c = 0; c < nChunks; ++c) {
-      const int64_t r0 = el.len * c / nChunks, r1 = el.len * (c + 1) / nChunks;
+      // cut at multiples of 8 rows (whole m8 DMMA fragments); only the last chunk is ragged
+      const int64_t r0 = std::min(el.len, (el.len * c / nChunks + 7) & ~int64_t(7));
+      const int64_t r1 = c + 1 == nChunks ? el.len : std::min(el.len, (el.len * (c + 1) / nChunks + 7) & ~int64_t(7));
       const int rows = (int)(r1 - r0);
       DevItem it{};
       it.outAddr = addrOf(el.buf, el.start + r0);
@@ -262,7 +264,9 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
           }
           const int64_t nK = (d.k + KC - 1) / KC;
           for (int64_t kk = 0; kk < nK; ++kk) {
-            const int64_t c0 = d.k * kk / nK, c1 = d.k * (kk + 1) / nK;
+            // pieces of whole k4 DMMA steps; only the last one is ragged
+            const int64_t c0 = std::min(d.k, (d.k * kk / nK + 3) & ~int64_t(3));
+            const int64_t c1 = kk + 1 == nK ? d.k : std::min(d.k, (d.k * (kk + 1) / nK + 3) & ~int64_t(3));
             DevTile t{addrOf(d.inBuf, d.inOff + c0), (uint16_t)(c1 - c0), (uint16_t)rows};
             S.tiles.push_back(t);
             S.pieces.push_back(PieceRef{frags[q].seq, (int32_t)rowInOp, (int32_t)c0});

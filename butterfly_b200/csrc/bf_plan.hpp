@@ -29,7 +29,7 @@ constexpr int kWarpsPerCta = 8;       // gemv kernel: one work queue per warp
 constexpr int kTileBytes = 8192;      // upper bound of one packed tile
 constexpr int kMaxRowsComplex = 32;   // R for complex items (8 lanes per row, 8 passes)
 constexpr int kMaxRowsReal = 16;      // R for real items (16 lanes per row, 8 passes)
-constexpr int kMaxKcComplex = 64;     // KC upper bound (8 register chunks of 8 lanes)
+constexpr int kMaxKcComplex = 32;     // KC upper bound (bounds the operand rows the DMMA kernel stages per tile)
 constexpr int kMaxKcReal = 128;       // (8 register chunks of 16 lanes)
 
 // Address of a row in one of three spaces, packed in 32 bits: space << 30 | row.
