@@ -255,26 +255,40 @@ def run_ours(args, rank, local_rank, world):
             pass
 
     extra = None
-    if not args.no_extra and nrhs == 1 and world == 1:
-        # side measurement: the 256-RHS block apply on the same operator (configs[2])
+    if not args.no_extra and nrhs == 1:
+        # side measurement: the 256-RHS block apply per GPU on the same operator (configs[2]), against
+        # the fp64 ceilings measured in this run on this device (register-resident DFMA / DMMA loops)
         try:
+            import ctypes as C
+
+            dfma, dmma = C.c_double(), C.c_double()
+            capi.check(capi.load_library().bfCudaMeasureFp64Peak(local_rank, C.byref(dfma), C.byref(dmma)), "bfCudaMeasureFp64Peak")
             nr = 256
             X = torch.randn(n, nr, dtype=torch.complex128, device="cuda")
             Y = torch.empty(n, nr, dtype=torch.complex128, device="cuda")
             plan.apply_device(X, Y, stream=stream)
-            torch.cuda.synchronize()
+            barrier()
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a0.record()
-            reps = 2
+            reps = 3
             for _ in range(reps):
                 plan.apply_device(X, Y, stream=stream)
             a1.record()
-            torch.cuda.synchronize()
+            barrier()
             ms = a0.elapsed_time(a1) / reps
-            extra = {"nrhs": nr, "ms_per_apply": ms, "gflops": 8.0 * E * nr / (ms * 1e-3) / 1e9, "matvecs_per_s": nr / (ms * 1e-3)}
+            if world > 1:
+                t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            tf = 8.0 * E * nr / (ms * 1e-3) / 1e12  # per GPU
+            extra = {"nrhs_per_gpu": nr, "ms_per_apply": ms, "gflops": tf * 1e3 * world, "matvecs_per_s": nr * world / (ms * 1e-3),
+                     "launches_per_apply": int(plan.last_launch_count),
+                     "roofline": {"bound": "fp64 tensor pipe (DMMA)", "kernel": "bfWideMmaStage<2>", "achieved": tf, "peak": dmma.value,
+                                  "unit": "TFLOP/s", "frac": tf / dmma.value if dmma.value else None,
+                                  "peak_source": "measured in this run (bfCudaMeasureFp64Peak: DMMA m8n8k4 loop)", "dfma_peak": dfma.value}}
             del X, Y
         except Exception as e:  # e.g. out of memory for the workspace
-            extra = {"nrhs": 256, "error": str(e)[:200]}
+            extra = {"nrhs_per_gpu": 256, "error": str(e)[:200]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

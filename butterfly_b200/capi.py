@@ -156,6 +156,7 @@ EXPORTED_SYMBOLS = [
     "bfCudaApplyDevice",
     "bfCudaApplyHost",
     "bfCudaPlanLastLaunchCount",
+    "bfCudaMeasureFp64Peak",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
@@ -239,6 +240,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaStatusString.restype = C.c_char_p
     lib.bfCudaLastErrorMessage.argtypes = []
     lib.bfCudaLastErrorMessage.restype = C.c_char_p
+    lib.bfCudaMeasureFp64Peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.bfCudaMeasureFp64Peak.restype = i32
     lib.bfCudaAbiVersion.argtypes = []
     lib.bfCudaAbiVersion.restype = i32
     if path is None:

@@ -201,6 +201,10 @@ BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **desc);
 void bfCudaRawOpsFree(BfCudaPlanDesc *desc);
 
 /* ---- misc ---------------------------------------------------------------------------------- */
+/* Measured fp64 ceilings of `device` (-1 = current) in TFLOP/s: a register-resident DFMA loop and a
+ * DMMA (mma.sync.m8n8k4.f64) loop, ~20 ms each.  The roofline denominators of the many-RHS apply
+ * (bench.py); not used by the apply itself. */
+BfCudaStatus bfCudaMeasureFp64Peak(int32_t device, double *dfmaTflops, double *dmmaTflops);
 const char *bfCudaStatusString(BfCudaStatus status);
 const char *bfCudaLastErrorMessage(void); /* thread-local, human-readable detail */
 int32_t bfCudaAbiVersion(void);
