@@ -148,18 +148,50 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   const int q = blockIdx.x * kWarpsPerCta + warp;
   if (q >= a.numQueues) return;
   const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
-  const uint32_t tEnd = a.qTileBegin[q + 1];
+  const uint32_t tBeg = a.qTileBegin[q], tEnd = a.qTileBegin[q + 1];
   if (iBeg == iEnd) return;
   const uint64_t pol = policyEvictFirst();
 
+  // Descriptor windows: lane l holds tiles[twBase + l] / tiles[twBase + 32 + l] (and the same for
+  // items), refilled 32 entries ahead of use, so that neither cursor ever waits on a table load —
+  // a descriptor is one shuffle away.
+  const uint64_t *tileTab = reinterpret_cast<const uint64_t *>(a.tiles);
+  const uint4 *itemTab = reinterpret_cast<const uint4 *>(a.items);
+  auto loadTiles = [&](uint32_t base) -> uint64_t { return base + lane < tEnd ? tileTab[base + lane] : 0ull; };
+  auto loadItems = [&](uint32_t base) -> uint4 { return base + lane < iEnd ? itemTab[base + lane] : make_uint4(0u, 0u, 0u, 0u); };
+  uint32_t twBase = tBeg, iwBase = iBeg;
+  uint64_t tw0 = loadTiles(twBase), tw1 = loadTiles(twBase + 32);
+  uint4 iw0 = loadItems(iwBase), iw1 = loadItems(iwBase + 32);
+  auto getTile = [&](uint32_t t) -> DevTile {
+    const uint32_t off = t - twBase; // warp-uniform
+    uint64_t v;
+    if (off < 32) v = __shfl_sync(0xffffffffu, tw0, off);
+    else if (off < 64) v = __shfl_sync(0xffffffffu, tw1, off - 32);
+    else v = tileTab[t]; // the producer ran far ahead over value-less tiles
+    DevTile d;
+    d.inAddr = (uint32_t)v; d.kc = (uint16_t)(v >> 32); d.rows = (uint16_t)(v >> 48);
+    return d;
+  };
+  auto getItem = [&](uint32_t i) -> DevItem {
+    if (i - iwBase >= 32) { iw0 = iw1; iwBase += 32; iw1 = loadItems(iwBase + 32); }
+    const uint32_t off = i - iwBase;
+    DevItem d;
+    d.outAddr = __shfl_sync(0xffffffffu, iw0.x, off);
+    d.tileBegin = __shfl_sync(0xffffffffu, iw0.y, off);
+    const uint32_t rf = __shfl_sync(0xffffffffu, iw0.z, off);
+    d.rows = (uint16_t)rf; d.flags = (uint16_t)(rf >> 16);
+    d.numTiles = __shfl_sync(0xffffffffu, iw0.w, off);
+    return d;
+  };
+
   // producer (lane 0 issues; every lane tracks the same scalars) and consumer cursors
-  uint32_t pT = a.qTileBegin[q], pSeq = 0, cSeq = 0;
+  uint32_t pT = tBeg, pSeq = 0, cSeq = 0;
   const unsigned char *pPool = a.pool + a.qPool16[q] * 16ull;
   const unsigned char *cPool = pPool;
 
   auto produce = [&]() {
     while (pT < tEnd) {
-      const DevTile t = a.tiles[pT];
+      const DevTile t = getTile(pT);
       ++pT;
       const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
       const unsigned char *src = pPool;
@@ -192,7 +224,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   const int g = lane / G, l = lane % G;
 #pragma unroll 1
   for (uint32_t i = iBeg; i < iEnd; ++i) {
-    const DevItem it = a.items[i];
+    const DevItem it = getItem(i);
     const int rows = it.rows;
     T acc[P];
 #pragma unroll
@@ -201,7 +233,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
 
 #pragma unroll 1
     for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
-      const DevTile tl = a.tiles[t];
+      if (t - twBase >= 32 && pT - twBase >= 32) { tw0 = tw1; twBase += 32; tw1 = loadTiles(twBase + 32); } // both cursors left window 0
+      const DevTile tl = getTile(t);
       const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
       if (tl.kc >= kKcDiag) {
         if (lane < rows) {
