@@ -25,7 +25,7 @@ struct StageLaunch {
 };
 
 // Shared-memory geometry of the 1-RHS kernel (one ring of kGemvSlots slots per warp).
-constexpr int kGemvSlots = 3;
+constexpr int kGemvSlots = 2;
 constexpr int kGemvXBytes = 1056;                        // x segment: 64 c128 / 128 f64 (+16 B slack)
 constexpr int kGemvSlotBytes = kTileBytes + kGemvXBytes; // 9248
 constexpr int kGemvSmemBytes = kWarpsPerCta * kGemvSlots * (kGemvSlotBytes + 8) + 128;

@@ -25,7 +25,7 @@
 namespace bfc {
 
 // ---- tiling constants shared by the compiler and the kernels --------------------------------
-constexpr int kWarpsPerCta = 8;       // gemv kernel: one work queue per warp
+constexpr int kWarpsPerCta = 12;      // gemv kernel: one work queue per warp
 constexpr int kTileBytes = 8192;      // upper bound of one packed tile
 constexpr int kMaxRowsComplex = 32;   // R for complex items (8 lanes per row, 8 passes)
 constexpr int kMaxRowsReal = 16;      // R for real items (16 lanes per row, 8 passes)
