@@ -10,6 +10,12 @@
                          BlockDiag] from bfFacHelm2Make) with its factor values, an operand
                          supported on its source box and the reference's bfMatMul result on its
                          target box.
+  lbo_stream_n600.npz    the REAL path: bfFacStreamer (src/fac_streamer.c:386) fed with the real
+                         spherical harmonics of degree <= 11 on 600 Fibonacci-sphere points through
+                         the restated body of bfLboFeedFacStreamerNextEigenband (src/lbo.c:96-137,
+                         oracle/ref_driver.c refStream*), tol 1e-3; the flattened bfFacSpanGetMat
+                         object WITH its factor values, a seeded operand pair and the reference's
+                         bfMatMulVec / bfMatRmulVec results.
 """
 import sys
 from pathlib import Path
@@ -101,6 +107,19 @@ def main():
     print("full: ops", raw.num_ops, "E", raw.num_entries, "| block:", sub.num_ops, "ops, E", sub.num_entries,
           "rows", (r0, r1), "cols", (c0, c1), "factors", len(sub.buf_rows) - 1)
     h.close()
+
+    # ---- real (streamed) path ----
+    st = reflib.sphere_stream(600, 11)
+    raw_s = st.flatten()
+    rng = np.random.default_rng(0)
+    xs_ = rng.standard_normal(st.num_cols)
+    vs_ = rng.standard_normal(st.num_rows)
+    ys_, _ = st.mulvec(xs_)
+    zs_, _ = st.mulvec(vs_, transposed=True)
+    raw_s.save(OUT / "lbo_stream_n600.npz")
+    np.savez_compressed(OUT / "lbo_stream_n600_io.npz", x=xs_, y=ys_, v=vs_, z=zs_, row_perm=st.row_perm(),
+                        bands=np.array(st.bands), fingerprint=raw_s.fingerprint())
+    print("stream: ops", raw_s.num_ops, "E", raw_s.num_entries, "shape", (st.num_rows, st.num_cols), "bands", st.bands)
 
 
 if __name__ == "__main__":

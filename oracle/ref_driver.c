@@ -160,3 +160,108 @@ int refOpenblasThreads(int n) {
   if (n > 0) openblas_set_num_threads(n);
   return openblas_get_num_threads();
 }
+
+/* ---- streamed (real, LBO-style) butterfly ----------------------------------------------------
+ * Restates the 40 lines of bfLboFeedFacStreamerNextEigenband (src/lbo.c:96-137) with the
+ * eigenband supplied by the caller instead of bfGetEigenband (ARPACK/UMFPACK are absent here,
+ * SURVEY.md §8c): octree row tree on the points (examples/covariance/lbo_cov.c:88-96), empty
+ * frequency interval tree of valence 2 (lbo_cov.c:113-116), BfFacSpec as lbo_cov.c:121-129,
+ * then per column leaf: insert the band's frequencies, permute the band's rows into row-tree
+ * order, bfFacStreamerFeed.  The result is bfFacSpanGetMat (lbo_cov.c:189-190). */
+#include <bf/fac_span.h>
+#include <bf/fac_streamer.h>
+#include <bf/interval_tree.h>
+#include <bf/interval_tree_node.h>
+#include <bf/octree.h>
+#include <bf/tree.h>
+#include <bf/tree_node.h>
+
+typedef struct RefStream {
+  BfPoints3 *points;
+  BfOctree octree;
+  BfTree *rowTree;
+  BfPerm *revRowPerm;
+  BfIntervalTree *freqTree;
+  BfPoints1 *freqs;
+  BfFacStreamer *streamer;
+  BfMat *Phi; /* bfFacSpanGetMat view, created on demand */
+  BfFacSpan *span;
+  int64_t n;
+} RefStream;
+
+RefStream *refStreamBegin(const double *xyz, int64_t n, double freqMax, int64_t freqTreeDepth, double tol,
+                          int64_t rowTreeOffset, int64_t minNumRows, int64_t minNumCols) {
+  RefStream *s = calloc(1, sizeof *s);
+  s->n = n;
+  s->points = bfPoints3NewWithDefaultCapacity();
+  for (int64_t i = 0; i < n; ++i) {
+    BfPoint3 p = {xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]};
+    bfPoints3Append(s->points, p);
+  }
+  bfOctreeInit(&s->octree, s->points, NULL, /* maxLeafSize: */ 1);
+  s->rowTree = bfOctreeToTree(&s->octree);
+  s->revRowPerm = bfPermGetReversePerm(bfTreeGetPermConst(s->rowTree));
+  if (freqTreeDepth < 0) freqTreeDepth = (int64_t)bfTreeGetMaxDepth(s->rowTree) - 3;
+  s->freqTree = bfIntervalTreeNew();
+  bfIntervalTreeInitEmpty(s->freqTree, 0, freqMax, 2, (BfSize)freqTreeDepth);
+  s->freqs = bfPoints1New();
+  bfPoints1InitEmpty(s->freqs, BF_ARRAY_DEFAULT_CAPACITY);
+  BfFacSpec spec = {
+    .rowTree = s->rowTree,
+    .colTree = bfIntervalTreeToTree(s->freqTree),
+    .rowTreeInitDepth = (BfSize)rowTreeOffset,
+    .colTreeInitDepth = (BfSize)freqTreeDepth,
+    .tol = tol,
+    .minNumRows = (BfSize)minNumRows,
+    .minNumCols = (BfSize)minNumCols,
+    .compareRelativeErrors = false,
+  };
+  s->streamer = bfFacStreamerNew();
+  bfFacStreamerInit(s->streamer, &spec);
+  return s;
+}
+
+int64_t refStreamRowTreeDepth(RefStream *s) { return (int64_t)bfTreeGetMaxDepth(s->rowTree); }
+void refStreamGetRowPerm(RefStream *s, int64_t *perm) {
+  BfPerm const *p = bfTreeGetPermConst(s->rowTree);
+  for (BfSize i = 0; i < p->size; ++i) perm[i] = (int64_t)p->index[i];
+}
+int refStreamIsDone(RefStream *s) { return bfFacStreamerIsDone(s->streamer) ? 1 : 0; }
+
+/* The frequency interval [a, b) of the column leaf the streamer expects next (src/lbo.c:40-66). */
+int refStreamCurrentBand(RefStream *s, double *a, double *b, int *leftmost, int *rightmost) {
+  BfTreeNode *node = bfFacStreamerGetCurrentColumnNode(s->streamer);
+  if (!node || !bfTreeNodeIsLeaf(node)) return 1;
+  BfIntervalTreeNode const *in = bfTreeNodeConstToIntervalTreeNodeConst(node);
+  *a = in->a; *b = in->b; *leftmost = in->isLeftmost; *rightmost = in->isRightmost;
+  return 0;
+}
+
+/* phi: n x m row-major band in ORIGINAL point order; freqs: its m frequencies, ascending. */
+int refStreamFeed(RefStream *s, const double *phi, int64_t m, const double *freqs) {
+  BfTreeNode *node = bfFacStreamerGetCurrentColumnNode(s->streamer);
+  BfPoints1 *newFreqs = bfPoints1New();
+  bfPoints1InitEmpty(newFreqs, BF_ARRAY_DEFAULT_CAPACITY);
+  for (int64_t j = 0; j < m; ++j) bfPoints1Append(newFreqs, freqs[j]);
+  bfPoints1InsertPointsSorted(s->freqs, newFreqs);
+  bfIntervalTreeSetPoints(s->freqTree, s->freqs, /* rebuildTree: */ false);
+  if ((int64_t)bfTreeNodeGetNumPoints(node) != m) { bfPoints1Delete(&newFreqs); return 2; } /* src/lbo.c:126 */
+  BfMatDenseReal *Phi = bfMatDenseRealNewZeros((BfSize)s->n, (BfSize)m);
+  for (int64_t i = 0; i < s->n; ++i)
+    memcpy(Phi->data + i * Phi->super.rowStride, phi + i * m, sizeof(double) * (size_t)m);
+  BfMat *PhiMat = bfMatDenseRealToMat(Phi);
+  bfMatPermuteRows(PhiMat, s->revRowPerm);
+  bfFacStreamerFeed(s->streamer, PhiMat);
+  bfMatDelete(&PhiMat);
+  bfPoints1Delete(&newFreqs);
+  return 0;
+}
+
+BfMat *refStreamGetMat(RefStream *s) {
+  if (!s->Phi) {
+    s->span = bfFacStreamerGetFacSpan(s->streamer);
+    s->Phi = bfFacSpanGetMat(s->span, BF_POLICY_VIEW);
+  }
+  return s->Phi;
+}
+int64_t refStreamNumFreqs(RefStream *s) { return (int64_t)s->freqs->size; }

@@ -171,3 +171,109 @@ def reverse_perm(perm: np.ndarray) -> np.ndarray:
 
 def set_blas_threads(n: int) -> int:
     return load().refOpenblasThreads(n)
+
+
+# ---- streamed real butterfly (LBO-style) -------------------------------
+def fibonacci_sphere(n: int) -> np.ndarray:
+    """n quasi-uniform points on the unit sphere (as tests/generate_data_for_test_linalg.py:29-32)."""
+    i = np.arange(n) + 0.5
+    phi = np.arccos(1 - 2 * i / n)
+    theta = np.pi * (1 + 5 ** 0.5) * i
+    return np.ascontiguousarray(np.stack([np.cos(theta) * np.sin(phi), np.sin(theta) * np.sin(phi), np.cos(phi)], axis=1))
+
+
+def real_sph_harm_band(points: np.ndarray, degrees) -> tuple[np.ndarray, np.ndarray]:
+    """Real spherical harmonics of the given degrees on unit-sphere points: the exact LBO
+    eigenfunctions of the sphere (eigenvalue l(l+1), frequency sqrt(l(l+1))).  Returns (n x m band,
+    m frequencies ascending)."""
+    from scipy.special import sph_harm_y
+
+    x, y, z = points.T
+    polar = np.arccos(np.clip(z, -1, 1))
+    azim = np.arctan2(y, x)
+    cols, freqs = [], []
+    for l in degrees:
+        for m in range(-l, l + 1):
+            Y = sph_harm_y(l, abs(m), polar, azim)
+            if m == 0:
+                c = Y.real
+            elif m > 0:
+                c = np.sqrt(2) * (-1) ** m * Y.real
+            else:
+                c = np.sqrt(2) * (-1) ** m * Y.imag
+            cols.append(c)
+            freqs.append(np.sqrt(l * (l + 1.0)))
+    if not cols:
+        return np.zeros((len(points), 0)), np.zeros(0)
+    return np.ascontiguousarray(np.stack(cols, axis=1)), np.asarray(freqs)
+
+
+class Stream:
+    """bfFacStreamer fed with caller-supplied eigenbands (oracle/ref_driver.c refStream*: the body
+    of bfLboFeedFacStreamerNextEigenband, src/lbo.c:96-137, minus the ARPACK call).  `band_fn(a, b,
+    leftmost, rightmost)` returns (n x m band in original point order, m ascending frequencies in
+    [a, b))."""
+
+    def __init__(self, points: np.ndarray, freq_max: float, band_fn, freq_tree_depth: int = -1, tol: float = 1e-3,
+                 row_tree_offset: int = 0, min_rows: int = 20, min_cols: int = 20):
+        self.drv = d = load()
+        vp, i64, dbl = C.c_void_p, C.c_int64, C.c_double
+        d.refStreamBegin.argtypes = [vp, i64, dbl, i64, dbl, i64, i64, i64]; d.refStreamBegin.restype = vp
+        d.refStreamRowTreeDepth.argtypes = [vp]; d.refStreamRowTreeDepth.restype = i64
+        d.refStreamGetRowPerm.argtypes = [vp, vp]; d.refStreamGetRowPerm.restype = None
+        d.refStreamIsDone.argtypes = [vp]; d.refStreamIsDone.restype = C.c_int
+        d.refStreamCurrentBand.argtypes = [vp, vp, vp, vp, vp]; d.refStreamCurrentBand.restype = C.c_int
+        d.refStreamFeed.argtypes = [vp, vp, i64, vp]; d.refStreamFeed.restype = C.c_int
+        d.refStreamGetMat.argtypes = [vp]; d.refStreamGetMat.restype = vp
+        d.refStreamNumFreqs.argtypes = [vp]; d.refStreamNumFreqs.restype = i64
+        pts = np.ascontiguousarray(points, dtype=np.float64)
+        self.n = len(pts)
+        self.h = d.refStreamBegin(pts.ctypes.data, self.n, float(freq_max), int(freq_tree_depth), float(tol),
+                                  int(row_tree_offset), int(min_rows), int(min_cols))
+        self.bands = []
+        while not d.refStreamIsDone(self.h):
+            a, b = C.c_double(), C.c_double()
+            lm, rm = C.c_int(), C.c_int()
+            if d.refStreamCurrentBand(self.h, C.byref(a), C.byref(b), C.byref(lm), C.byref(rm)):
+                raise RuntimeError("streamer has no current column leaf")
+            band, freqs = band_fn(a.value, b.value, bool(lm.value), bool(rm.value))
+            band = np.ascontiguousarray(band, dtype=np.float64)
+            freqs = np.ascontiguousarray(freqs, dtype=np.float64)
+            rc = d.refStreamFeed(self.h, band.ctypes.data, band.shape[1], freqs.ctypes.data)
+            if rc:
+                raise RuntimeError(f"refStreamFeed: {rc} (band [{a.value}, {b.value}) with {band.shape[1]} columns)")
+            self.bands.append((a.value, b.value, band.shape[1]))
+        self.mat = d.refStreamGetMat(self.h)
+        self.num_rows = d.refMatNumRows(self.mat)
+        self.num_cols = d.refMatNumCols(self.mat)
+
+    def row_perm(self) -> np.ndarray:
+        p = np.zeros(self.n, np.int64)
+        self.drv.refStreamGetRowPerm(self.h, p.ctypes.data)
+        return p
+
+    def mulvec(self, x: np.ndarray, transposed: bool = False):
+        """bfMatMulVec / bfMatRmulVec through the object's CURRENT vtable.  Returns (y, seconds)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.zeros(self.num_cols if transposed else self.num_rows)
+        t = self.drv.refMatMulVecReal(self.mat, x.ctypes.data, len(x), y.ctypes.data, int(transposed))
+        return y, t
+
+    flatten = Helm2.flatten
+    attach = Helm2.attach
+    detach = Helm2.detach
+
+
+def sphere_stream(n: int = 4000, lmax: int = 31, tol: float = 1e-3, freq_tree_depth: int = -1) -> "Stream":
+    """The survey's streamed-factorization probe: n Fibonacci-sphere points, real spherical harmonics
+    of degree <= lmax grouped into the frequency tree's leaf bands."""
+    pts = fibonacci_sphere(n)
+    fmax = np.sqrt(lmax * (lmax + 1.0)) + 0.25
+
+    def band_fn(a, b, leftmost, rightmost):
+        degs = [l for l in range(lmax + 1) if (leftmost or np.sqrt(l * (l + 1.0)) >= a) and (rightmost or np.sqrt(l * (l + 1.0)) < b)]
+        return real_sph_harm_band(pts, degs)
+
+    s = Stream(pts, fmax, band_fn, freq_tree_depth=freq_tree_depth, tol=tol)
+    s.points = pts
+    return s

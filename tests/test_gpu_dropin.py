@@ -76,3 +76,40 @@ def test_fused_tree_permutation_matches_bfMatPermuteRows():
             assert np.array_equal(plan.apply_host(x), want)
     finally:
         h.close()
+
+
+# ---- real path (configs[3]: LBO-style streamed butterfly, forward and transpose) ------------------
+def test_golden_stream_on_gpu():
+    """The streamed real operator with the reference's factor values, against the reference's own
+    bfMatMulVec / bfMatRmulVec outputs (tests/golden, no reference needed at run time)."""
+    raw = RawOps.load(G / "lbo_stream_n600.npz")
+    io = np.load(G / "lbo_stream_n600_io.npz")
+    with Plan(raw, build_transpose=1) as plan:
+        y = plan.apply_host(io["x"], capi.OP_N)
+        z = plan.apply_host(io["v"], capi.OP_T)
+        assert np.linalg.norm(y - io["y"]) / np.linalg.norm(io["y"]) <= TOL
+        assert np.linalg.norm(z - io["z"]) / np.linalg.norm(io["z"]) <= TOL
+        # a block of RHS (no reference equivalent: bfMatDenseRealMul is BF_DIE, SURVEY F4): columns independent
+        X = np.stack([io["x"], -2.0 * io["x"], np.roll(io["x"], 5)], axis=1)
+        Y = plan.apply_host(X, capi.OP_N)
+        assert np.linalg.norm(Y[:, 0] - io["y"]) / np.linalg.norm(io["y"]) <= TOL
+        assert np.linalg.norm(Y[:, 1] + 2.0 * io["y"]) / np.linalg.norm(io["y"]) <= 2 * TOL
+
+
+@needs_ref
+def test_mulvec_rmulvec_through_swapped_vtable():
+    """bfMatMulVec(Phi, x) / bfMatRmulVec(Phi, v) (examples/covariance/lbo_cov.c:41,51,56) on a live
+    bfFacStreamer factorization: CPU reference vs the same calls after bfCudaMatAttach."""
+    s = reflib.sphere_stream(1500, 15)
+    rng = np.random.default_rng(3)
+    x, v = rng.standard_normal(s.num_cols), rng.standard_normal(s.num_rows)
+    y_cpu, _ = s.mulvec(x)
+    z_cpu, _ = s.mulvec(v, transposed=True)
+    s.attach(build_transpose=1)
+    y_gpu, _ = s.mulvec(x)
+    z_gpu, _ = s.mulvec(v, transposed=True)
+    s.detach()
+    y_back, _ = s.mulvec(x)
+    assert np.linalg.norm(y_gpu - y_cpu) / np.linalg.norm(y_cpu) <= TOL
+    assert np.linalg.norm(z_gpu - z_cpu) / np.linalg.norm(z_cpu) <= TOL
+    assert np.array_equal(y_back, y_cpu)

@@ -67,3 +67,39 @@ def test_raw_ops_file_roundtrip(block, lib, tmp_path):
     assert np.array_equal(back.buf_rows, raw.buf_rows)
     assert np.array_equal(portlib.apply(back, x), portlib.apply(raw, x))
     assert lib.bfCudaRawOpsLoad(str(tmp_path / "missing").encode(), C.byref(out)) == 6  # BF_CUDA_ERROR_IO
+
+
+# ---- real (streamed, LBO-style) path: bfMatMulVec / bfMatRmulVec of the reference ----------------
+@pytest.fixture(scope="module")
+def stream():
+    raw = RawOps.load(G / "lbo_stream_n600.npz")
+    io = np.load(G / "lbo_stream_n600_io.npz")
+    return raw, io
+
+
+def test_port_oracle_reproduces_reference_mulvec_and_rmulvec(stream):
+    raw, io = stream
+    assert raw.dtype == capi.REAL_F64 and (raw.num_rows, raw.num_cols) == (600, 144)
+    assert np.array_equal(raw.fingerprint(), io["fingerprint"])
+    y = portlib.apply(raw, io["x"][:, None], capi.OP_N)[:, 0]
+    z = portlib.apply(raw, io["v"][:, None], capi.OP_T)[:, 0]
+    assert np.linalg.norm(y - io["y"]) / np.linalg.norm(io["y"]) < 1e-13   # bfMatMulVec, src/mat_product.c:247
+    assert np.linalg.norm(z - io["z"]) / np.linalg.norm(io["z"]) < 1e-13   # bfMatRmulVec, src/mat_product.c:312
+
+
+@pytest.mark.parametrize("op,xin,yout", [(capi.OP_N, "x", "y"), (capi.OP_T, "v", "z")])
+def test_compiled_tables_reproduce_reference_real_path(stream, op, xin, yout):
+    raw, io = stream
+    t = Tables(raw, op, 148 * 12)
+    try:
+        t.check_queues()
+        y = t.apply(io[xin])[:, 0]
+    finally:
+        t.close()
+    assert np.linalg.norm(y - io[yout]) / np.linalg.norm(io[yout]) < 1e-13
+
+
+def test_streamed_operator_contains_identity_leaves(stream):
+    raw, _ = stream
+    kinds = set(raw.ops["kind"].tolist())
+    assert capi.LEAF_IDENTITY in kinds and capi.LEAF_DENSE in kinds  # pass-through Psi / W blocks, src/fac.c:649-676

@@ -62,3 +62,48 @@ def test_butterfly_vs_dense_kernel_pin(helm):
     y, _ = helm.matmul(x)
     yd = helm.dense_kernel() @ x
     assert np.linalg.norm(y[:, 0] - yd) / np.linalg.norm(yd) < 1e-11
+
+
+# ---- real (streamed) path: live bfFacStreamer factorization --------------------------------------
+@pytest.fixture(scope="module")
+def stream():
+    return reflib.sphere_stream(600, 11)
+
+
+def test_stream_flatten_matches_golden_structure(stream):
+    io = np.load(G / "lbo_stream_n600_io.npz")
+    raw = stream.flatten()
+    assert np.array_equal(raw.fingerprint(), io["fingerprint"]), "flattened index tables changed"
+    assert np.array_equal(stream.row_perm(), io["row_perm"])
+    y, _ = stream.mulvec(io["x"])
+    z, _ = stream.mulvec(io["v"], transposed=True)
+    assert np.linalg.norm(y - io["y"]) <= 1e-14 * np.linalg.norm(io["y"])
+    assert np.linalg.norm(z - io["z"]) <= 1e-14 * np.linalg.norm(io["z"])
+
+
+def test_stream_port_and_tables_match_reference_mulvec_rmulvec(stream):
+    rng = np.random.default_rng(5)
+    raw = stream.flatten()
+    for op, n_in, transposed in ((capi.OP_N, stream.num_cols, False), (capi.OP_T, stream.num_rows, True)):
+        x = rng.standard_normal(n_in)
+        y_ref, _ = stream.mulvec(x, transposed=transposed)
+        y_port = portlib.apply(raw, x[:, None], op)[:, 0]
+        assert np.linalg.norm(y_port - y_ref) / np.linalg.norm(y_ref) < 1e-13
+        t = Tables(raw, op, 148 * 12)
+        try:
+            y_tab = t.apply(x)[:, 0]
+        finally:
+            t.close()
+        assert np.linalg.norm(y_tab - y_ref) / np.linalg.norm(y_ref) < 1e-13
+
+
+def test_stream_vs_dense_band_pin(stream):
+    """The streamer's own self-check (src/fac_streamer.c:286-301): butterfly vs the dense band it was
+    fed, to about the SVD truncation tolerance (1e-3)."""
+    B, _ = reflib.real_sph_harm_band(stream.points, range(12))
+    rev = reflib.reverse_perm(stream.row_perm())
+    Bp = np.zeros_like(B)
+    Bp[rev] = B  # rows into row-tree order: out[rev[i]] = in[i]
+    x = np.random.default_rng(1).standard_normal(stream.num_cols)
+    y, _ = stream.mulvec(x)
+    assert np.abs(y - Bp @ x).max() / np.abs(Bp @ x).max() < 5e-3
