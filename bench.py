@@ -30,7 +30,7 @@ CPU_SAMPLE_N = 8192
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=int(os.environ.get("BF_BENCH_N", DEFAULT_N)))
@@ -66,7 +66,7 @@ class ClockSampler:
                     self.samples.append([s.strip() for s in out.split(",")])
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.02)
 
     def __enter__(self):
         self.t = threading.Thread(target=self._run, daemon=True)

@@ -387,12 +387,18 @@ BfCudaStatus bfCudaApplyHost(BfCudaPlan *P, int32_t op, const void *x, int64_t l
   if (st != BF_CUDA_OK) return st;
   st = ensureBytes(&P->ioY, &P->ioYBytes, std::max<size_t>((size_t)D.rowsOut * rowBytes, 16));
   if (st != BF_CUDA_OK) return st;
-  if (D.rowsIn > 0)
-    BF_CUDA_TRY(cudaMemcpy2DAsync(P->ioX, rowBytes, x, (size_t)ldx * es, rowBytes, (size_t)D.rowsIn, cudaMemcpyHostToDevice, P->stream));
+  // dense operands (ld == nrhs, the reference's own layout: rowStride == numCols) move as ONE linear
+  // copy; a 2-D copy of 16-byte rows runs at a fraction of PCIe bandwidth
+  if (D.rowsIn > 0) {
+    if (ldx == nrhs) BF_CUDA_TRY(cudaMemcpyAsync(P->ioX, x, (size_t)D.rowsIn * rowBytes, cudaMemcpyHostToDevice, P->stream));
+    else BF_CUDA_TRY(cudaMemcpy2DAsync(P->ioX, rowBytes, x, (size_t)ldx * es, rowBytes, (size_t)D.rowsIn, cudaMemcpyHostToDevice, P->stream));
+  }
   st = bfCudaApplyDevice(P, op, P->ioX, nrhs, nrhs, P->ioY, nrhs, P->stream);
   if (st != BF_CUDA_OK) return st;
-  if (D.rowsOut > 0)
-    BF_CUDA_TRY(cudaMemcpy2DAsync(y, (size_t)ldy * es, P->ioY, rowBytes, rowBytes, (size_t)D.rowsOut, cudaMemcpyDeviceToHost, P->stream));
+  if (D.rowsOut > 0) {
+    if (ldy == nrhs) BF_CUDA_TRY(cudaMemcpyAsync(y, P->ioY, (size_t)D.rowsOut * rowBytes, cudaMemcpyDeviceToHost, P->stream));
+    else BF_CUDA_TRY(cudaMemcpy2DAsync(y, (size_t)ldy * es, P->ioY, rowBytes, rowBytes, (size_t)D.rowsOut, cudaMemcpyDeviceToHost, P->stream));
+  }
   BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
   return BF_CUDA_OK;
 }
