@@ -290,6 +290,37 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:  # e.g. out of memory for the workspace
             extra = {"nrhs_per_gpu": 256, "error": str(e)[:200]}
 
+    lbo = None
+    if not args.no_extra and nrhs == 1 and world == 1:
+        # side measurement, configs[3]: real fp64 eigenbasis butterfly, forward and transposed 1-RHS apply
+        try:
+            rawL, metaL = workloads.lbo_like()
+            planL = Plan(rawL, device=local_rank, build_transpose=1)
+            planL.fill_synthetic(7)
+            EL = planL.info["numEntries"]
+            lbo = {"workload": metaL["workload"], "structure": metaL["structure"], "E": int(EL), "dtype": "f64"}
+            for name, op, n_in, n_out in (("forward", capi.OP_N, rawL.num_cols, rawL.num_rows), ("transpose", capi.OP_T, rawL.num_rows, rawL.num_cols)):
+                xv = torch.randn(n_in, 1, dtype=torch.float64, device="cuda")
+                yv = torch.empty(n_out, 1, dtype=torch.float64, device="cuda")
+                for _ in range(3):
+                    planL.apply_device(xv, yv, op=op, stream=stream)
+                torch.cuda.synchronize()
+                b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                reps = 20
+                b0.record()
+                for _ in range(reps):
+                    planL.apply_device(xv, yv, op=op, stream=stream)
+                b1.record()
+                torch.cuda.synchronize()
+                ms = b0.elapsed_time(b1) / reps
+                byts = 8.0 * EL + 8.0 * (n_in + n_out)
+                lbo[name] = {"ms_per_apply": ms, "gflops": 2.0 * EL / (ms * 1e-3) / 1e9, "matvecs_per_s": 1e3 / ms,
+                             "gbs": byts / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": byts / (ms * 1e-3) / 1e9 / peaks()[0],
+                             "launches": int(planL.last_launch_count)}
+            planL.close()
+        except Exception as e:
+            lbo = {"error": str(e)[:200]}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference_leg(steps=10, warmup=2)
@@ -314,6 +345,7 @@ def run_ours(args, rank, local_rank, world):
             "roofline": roof,
             "cpu_baseline": cpu,
             "rhs256": extra,
+            "lbo_real": lbo,
         }
         print(json.dumps(line), flush=True)
     plan.close()

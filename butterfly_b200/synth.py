@@ -173,3 +173,18 @@ def random_rect(num_rows=700, num_cols=300, dtype=capi.REAL_F64, seed=0, with_va
     for j in range(ncb):
         b.dense(t, int(offs[j]), 1, int(redges[j]), int(redges[j + 1] - redges[j]), int(ranks[j]))
     return b.finish(num_rows, num_cols)
+
+
+def lbo_like(num_rows=500_000, num_eigs=4096, bands=16, depth=5, rank_lo=20, rank_hi=44, dtype=capi.REAL_F64,
+             seed=0, with_values=False) -> RawOps:
+    """Shape of a streamed LBO eigenbasis butterfly (bfFacSpanGetMat, src/fac_span.c:126-155): a
+    1 x bands MatBlockDense whose blocks are MatProducts mapping one frequency band (a contiguous
+    run of eigenvector columns) to ALL vertices through `depth` butterfly levels.  Structure only
+    (values filled on the device) unless with_values; stands in for configs[3] at sizes the
+    reference's CPU streamer cannot reach in bench time (169 s already at 4000 x 1024)."""
+    rng = np.random.default_rng(seed)
+    b = _Builder(dtype, with_values, rng)
+    edges = np.linspace(0, num_eigs, bands + 1).round().astype(np.int64)
+    for j in range(bands):
+        _butterfly(b, 0, (int(edges[j]), int(edges[j + 1])), 1, (0, num_rows), depth, rank_lo, rank_hi, False)
+    return b.finish(num_rows, num_eigs)

@@ -43,3 +43,10 @@ def helm2_circle(n: int, k: float | None = None, cache_dir: str | None = None):
     meta["perm"] = z["perm"]
     meta["structure_seconds"] = float(z["seconds"])
     return raw, meta
+
+
+def lbo_like(num_rows: int = 500_000, num_eigs: int = 4096):
+    """configs[3] stand-in: real fp64 eigenbasis butterfly of the streamed shape (synth.lbo_like)."""
+    raw = synth.lbo_like(num_rows, num_eigs)
+    return raw, {"workload": f"lbo_like {num_rows} vertices x {num_eigs} eigenvectors, 16 bands, depth 5, ranks 20-44",
+                 "structure": "synthetic streamed-butterfly shape (values synthetic)"}
