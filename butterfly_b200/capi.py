@@ -157,6 +157,8 @@ EXPORTED_SYMBOLS = [
     "bfCudaApplyHost",
     "bfCudaPlanLastLaunchCount",
     "bfCudaMeasureFp64Peak",
+    "bfCudaPlanGetStream",
+    "bfCudaSolveGMRES",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
@@ -242,6 +244,10 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaLastErrorMessage.restype = C.c_char_p
     lib.bfCudaMeasureFp64Peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.bfCudaMeasureFp64Peak.restype = i32
+    lib.bfCudaPlanGetStream.argtypes = [vp]
+    lib.bfCudaPlanGetStream.restype = vp
+    lib.bfCudaSolveGMRES.argtypes = [vp, vp, vp, C.c_double, i64, vp, C.POINTER(i64), C.POINTER(C.c_double), C.POINTER(i64)]
+    lib.bfCudaSolveGMRES.restype = i32
     lib.bfCudaAbiVersion.argtypes = []
     lib.bfCudaAbiVersion.restype = i32
     if path is None:

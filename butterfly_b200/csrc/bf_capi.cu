@@ -262,6 +262,7 @@ BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *P, int32_t enable) {
 }
 
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *P) { return P ? P->lastLaunches : 0; }
+void *bfCudaPlanGetStream(const BfCudaPlan *P) { return P ? (void *)P->stream : nullptr; }
 
 BfCudaStatus bfCudaPlanGetStageTimes(BfCudaPlan *P, float *ms, int64_t capacity, int64_t *numStages) {
   if (!P || !numStages) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");

@@ -1,0 +1,250 @@
+// bf_gmres.cu — device-resident GMRES around the butterfly apply.
+//
+// Restates bfSolveGMRES (src/linalg.c:47-318) for one complex right-hand side and no preconditioner:
+// modified Gram-Schmidt Arnoldi (src/linalg.c:155-190), Givens rotations computed the way
+// bfVecComplexGetGivensRotation does (src/vec_complex.c:230-290) and applied as
+// mulInplace_givensComplex does (src/vec_complex.c:155-168), the convergence test
+// |s[j+1]| / beta < tol (src/linalg.c:224-231) and the reconstruction from the first j basis vectors
+// (src/linalg.c:237-281 — when the test fires at column j the reference leaves the loop BEFORE
+// counting that column, so the returned iterate uses j columns; we do the same).
+//
+// The reference round-trips every Krylov vector through host malloc and does the Gram-Schmidt with
+// scalar loops.  Here the basis V, the work vector and all dots stay in HBM; each Gram-Schmidt step
+// is ONE kernel (reduce the previous step's partial dots -> h_i, w -= h_i v_i, partial dots against
+// v_{i+1}), reductions are two-stage and fixed-order (deterministic), and only the j + 2 entries of
+// the new Hessenberg column cross PCIe per iteration.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <complex>
+#include <string>
+#include <vector>
+
+#include "bf_cuda.h"
+
+namespace {
+constexpr int kBlocks = 148 * 4;
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ double2 blockSum(double2 v, double2 *sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+  }
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) sh[w] = v;
+  __syncthreads();
+  double2 t = make_double2(0.0, 0.0);
+  for (int i = 0; i < kThreads / 32; ++i) { t.x += sh[i].x; t.y += sh[i].y; } // same order in every thread
+  return t;
+}
+// Total of `num` partials, identical in every thread of every block (fixed order).
+__device__ __forceinline__ double2 totalOf(const double2 *partials, int num, double2 *sh) {
+  double2 v = make_double2(0.0, 0.0);
+  for (int i = threadIdx.x; i < num; i += kThreads) { v.x += partials[i].x; v.y += partials[i].y; }
+  return blockSum(v, sh);
+}
+
+// partials[b] = sum over the block's elements of conj(v) * w   (zdotc, src/mat_dense_complex.c:115-121)
+// or of |w|^2 when v == NULL.
+__device__ __forceinline__ void dotInto(const double2 *v, const double2 *w, long long n, double2 *partials, double2 *sh) {
+  double2 acc = make_double2(0.0, 0.0);
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    const double2 b = w[k];
+    if (v) {
+      const double2 a = v[k];
+      acc.x += a.x * b.x + a.y * b.y;
+      acc.y += a.x * b.y - a.y * b.x;
+    } else {
+      acc.x += b.x * b.x + b.y * b.y;
+    }
+  }
+  acc = blockSum(acc, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+}
+
+__global__ void __launch_bounds__(kThreads) gmresDot(const double2 *v, const double2 *w, long long n, double2 *partials) {
+  __shared__ double2 sh[kThreads / 32];
+  dotInto(v, w, n, partials, sh);
+}
+
+// h = total(partialsIn); hOut = h; w -= h * vi; partialsOut = <vNext, w> (or |w|^2 when vNext == NULL)
+__global__ void __launch_bounds__(kThreads) gmresOrthoStep(const double2 *partialsIn, int numPartials, const double2 *vi,
+                                                            double2 *w, const double2 *vNext, long long n,
+                                                            double2 *partialsOut, double2 *hOut) {
+  __shared__ double2 sh[kThreads / 32];
+  const double2 h = totalOf(partialsIn, numPartials, sh);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *hOut = h;
+  double2 acc = make_double2(0.0, 0.0);
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    const double2 a = vi[k];
+    double2 b = w[k];
+    b.x -= h.x * a.x - h.y * a.y;
+    b.y -= h.x * a.y + h.y * a.x;
+    w[k] = b;
+    if (vNext) {
+      const double2 c = vNext[k];
+      acc.x += c.x * b.x + c.y * b.y;
+      acc.y += c.x * b.y - c.y * b.x;
+    } else {
+      acc.x += b.x * b.x + b.y * b.y;
+    }
+  }
+  acc = blockSum(acc, sh);
+  if (threadIdx.x == 0) partialsOut[blockIdx.x] = acc;
+}
+
+// nrm = sqrt(total(partials).x); normOut = nrm; out = (src - sub) / nrm   (sub may be NULL)
+__global__ void __launch_bounds__(kThreads) gmresNormalize(const double2 *partials, int numPartials, const double2 *src,
+                                                            const double2 *sub, long long n, double2 *out, double2 *normOut) {
+  __shared__ double2 sh[kThreads / 32];
+  const double nrm = sqrt(totalOf(partials, numPartials, sh).x);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *normOut = make_double2(nrm, 0.0);
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    double2 a = src[k];
+    out[k] = make_double2(a.x / nrm, a.y / nrm);
+  }
+}
+
+__global__ void gmresSub(const double2 *a, const double2 *b, long long n, double2 *out) { // out = a - b
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
+    out[k] = make_double2(a[k].x - b[k].x, a[k].y - b[k].y);
+}
+
+// x = x0 + sum_{i<m} y[i] * V[i]   (src/linalg.c:268-272)
+__global__ void gmresCombine(const double2 *V, long long n, const double2 *y, int m, const double2 *x0, double2 *x) {
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+    double2 acc = make_double2(0.0, 0.0);
+    for (int i = 0; i < m; ++i) {
+      const double2 v = V[(long long)i * n + k], c = y[i];
+      acc.x += c.x * v.x - c.y * v.y;
+      acc.y += c.x * v.y + c.y * v.x;
+    }
+    if (x0) { acc.x += x0[k].x; acc.y += x0[k].y; }
+    x[k] = acc;
+  }
+}
+
+using cplx = std::complex<double>;
+struct Givens { cplx c, s; };
+// src/vec_complex.c:276-287
+Givens makeGivens(cplx a, cplx b) {
+  Givens g;
+  if (std::abs(b) == 0) { g.c = 1; g.s = 0; }
+  else if (std::abs(b) > std::abs(a)) { cplx t = -a / b; g.s = 1.0 / std::sqrt(1 + std::pow(std::abs(t), 2)); g.c = t * g.s; }
+  else { cplx t = -b / a; g.c = 1.0 / std::sqrt(1 + std::pow(std::abs(t), 2)); g.s = t * g.c; }
+  return g;
+}
+// src/vec_complex.c:155-168
+void applyGivens(const Givens &g, cplx &z0, cplx &z1) {
+  const cplx a = z0, b = z1;
+  z0 = std::conj(g.c) * a + -g.s * b;
+  z1 = g.s * a + g.c * b;
+}
+} // namespace
+
+#define GM_TRY(expr)                                                                              \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess) { st = e_ == cudaErrorMemoryAllocation ? BF_CUDA_ERROR_OUT_OF_MEMORY : BF_CUDA_ERROR_RUNTIME; goto done; } \
+  } while (0)
+
+extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, double tol, int64_t maxNumIter,
+                                         void *x, int64_t *numIter, double *relResidual, int64_t *numApplies) {
+  if (!plan || !b || !x || maxNumIter <= 0) return BF_CUDA_ERROR_INVALID_ARGUMENT; // src/linalg.c:80-81
+  BfCudaPlanInfo info;
+  BfCudaStatus st = bfCudaPlanGetInfo(plan, &info);
+  if (st != BF_CUDA_OK) return st;
+  if (info.dtype != BF_CUDA_COMPLEX_F64) return BF_CUDA_ERROR_NOT_IMPLEMENTED;
+  if (info.numRows != info.numCols) return BF_CUDA_ERROR_INVALID_ARGUMENT; // src/linalg.c:85-86
+  const long long n = info.numRows;
+  const int m = (int)maxNumIter;
+  int prevDev = -1;
+  cudaGetDevice(&prevDev);
+  if (prevDev != info.device) cudaSetDevice(info.device);
+  cudaStream_t stream = (cudaStream_t)bfCudaPlanGetStream(plan);
+  double2 *V = nullptr, *w = nullptr, *partials = nullptr, *hcol = nullptr, *dx0 = nullptr, *dy = nullptr;
+  std::vector<cplx> S((size_t)m + 1, cplx(0)), hhost((size_t)m + 2), Hall((size_t)m * ((size_t)m + 1), cplx(0));
+  std::vector<Givens> J;
+  double beta = 0.0, residual = 0.0;
+  int64_t applies = 0;
+  int j = 0;
+  bool converged = false;
+  const size_t vecBytes = (size_t)n * sizeof(double2);
+  GM_TRY(cudaMalloc(&V, ((size_t)m + 1) * vecBytes));
+  GM_TRY(cudaMalloc(&w, vecBytes));
+  GM_TRY(cudaMalloc(&partials, 2 * kBlocks * sizeof(double2)));
+  GM_TRY(cudaMalloc(&hcol, ((size_t)m + 2) * sizeof(double2)));
+  GM_TRY(cudaMalloc(&dy, ((size_t)m + 1) * sizeof(double2)));
+  // R = B - A X0 (src/linalg.c:124-129); X0 == NULL is the zero iterate, for which A X0 == 0 exactly
+  GM_TRY(cudaMemcpyAsync(w, b, vecBytes, cudaMemcpyHostToDevice, stream));
+  if (x0) {
+    GM_TRY(cudaMalloc(&dx0, vecBytes));
+    GM_TRY(cudaMemcpyAsync(dx0, x0, vecBytes, cudaMemcpyHostToDevice, stream));
+    st = bfCudaApplyDevice(plan, BF_CUDA_OP_N, dx0, 1, 1, V, 1, stream); // V[0] as scratch
+    if (st != BF_CUDA_OK) goto done;
+    ++applies;
+    gmresSub<<<kBlocks, kThreads, 0, stream>>>(w, V, n, w);
+  }
+  // beta = ||r||, V[0] = r / beta, S = beta e1 (src/linalg.c:136-148)
+  gmresDot<<<kBlocks, kThreads, 0, stream>>>(nullptr, w, n, partials);
+  gmresNormalize<<<kBlocks, kThreads, 0, stream>>>(partials, kBlocks, w, nullptr, n, V, hcol);
+  GM_TRY(cudaMemcpyAsync(hhost.data(), hcol, sizeof(double2), cudaMemcpyDeviceToHost, stream));
+  GM_TRY(cudaStreamSynchronize(stream));
+  beta = hhost[0].real();
+  S[0] = beta;
+  if (!(beta > 0.0)) { // zero residual: the initial iterate is the solution
+    converged = true;
+  }
+  for (j = 0; j < m && !converged; ++j) {
+    double2 *Vj = V + (size_t)j * n;
+    st = bfCudaApplyDevice(plan, BF_CUDA_OP_N, Vj, 1, 1, w, 1, stream); // W = A V[j] (src/linalg.c:155)
+    if (st != BF_CUDA_OK) goto done;
+    ++applies;
+    // modified Gram-Schmidt (src/linalg.c:172-186), one kernel per basis vector
+    double2 *pIn = partials, *pOut = partials + kBlocks;
+    gmresDot<<<kBlocks, kThreads, 0, stream>>>(V, w, n, pIn);
+    for (int i = 0; i <= j; ++i) {
+      const double2 *vNext = i < j ? V + (size_t)(i + 1) * n : nullptr;
+      gmresOrthoStep<<<kBlocks, kThreads, 0, stream>>>(pIn, kBlocks, V + (size_t)i * n, w, vNext, n, pOut, hcol + i);
+      std::swap(pIn, pOut);
+    }
+    // H[j+1, j] = ||w||, V[j+1] = w / ||w|| (src/linalg.c:188-202)
+    gmresNormalize<<<kBlocks, kThreads, 0, stream>>>(pIn, kBlocks, w, nullptr, n, V + (size_t)(j + 1) * n, hcol + j + 1);
+    GM_TRY(cudaGetLastError());
+    GM_TRY(cudaMemcpyAsync(hhost.data(), hcol, ((size_t)j + 2) * sizeof(double2), cudaMemcpyDeviceToHost, stream));
+    GM_TRY(cudaStreamSynchronize(stream));
+    // previous rotations, the new one, the rotated right-hand side (src/linalg.c:206-231)
+    for (int i = 0; i < j; ++i) applyGivens(J[(size_t)i], hhost[(size_t)i], hhost[(size_t)i + 1]);
+    J.push_back(makeGivens(hhost[(size_t)j], hhost[(size_t)j + 1]));
+    applyGivens(J.back(), hhost[(size_t)j], hhost[(size_t)j + 1]);
+    applyGivens(J.back(), S[(size_t)j], S[(size_t)j + 1]);
+    for (int i = 0; i <= j; ++i) Hall[(size_t)j * ((size_t)m + 1) + i] = hhost[(size_t)i];
+    residual = std::abs(S[(size_t)j + 1]) / beta;
+    if (residual < tol) { converged = true; break; } // leaves j uncounted, as the reference does
+  }
+  {
+    // back substitution on the leading j x j triangle (src/linalg.c:240-266), x = x0 + V[:, :j] y
+    std::vector<cplx> y((size_t)std::max(j, 1), cplx(0));
+    for (int r = j - 1; r >= 0; --r) {
+      cplx acc = S[(size_t)r];
+      for (int c = r + 1; c < j; ++c) acc -= Hall[(size_t)c * ((size_t)m + 1) + r] * y[(size_t)c];
+      y[(size_t)r] = acc / Hall[(size_t)r * ((size_t)m + 1) + r];
+    }
+    if (j > 0) GM_TRY(cudaMemcpyAsync(dy, y.data(), (size_t)j * sizeof(double2), cudaMemcpyHostToDevice, stream));
+    gmresCombine<<<kBlocks, kThreads, 0, stream>>>(V, n, dy, j, dx0, w);
+    GM_TRY(cudaGetLastError());
+    GM_TRY(cudaMemcpyAsync(x, w, vecBytes, cudaMemcpyDeviceToHost, stream));
+    GM_TRY(cudaStreamSynchronize(stream));
+  }
+  if (numIter) *numIter = j;
+  if (relResidual) *relResidual = residual;
+  if (numApplies) *numApplies = applies;
+  st = BF_CUDA_OK;
+done:
+  cudaFree(V); cudaFree(w); cudaFree(partials); cudaFree(hcol); cudaFree(dx0); cudaFree(dy);
+  if (prevDev >= 0 && prevDev != info.device) cudaSetDevice(prevDev);
+  return st;
+}

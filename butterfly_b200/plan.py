@@ -122,6 +122,20 @@ class Plan:
         )
         return y[:, 0] if squeeze and out is None else y
 
+    def solve_gmres(self, b: np.ndarray, x0: np.ndarray | None = None, tol: float = 1e-12, max_iter: int = 50):
+        """bfCudaSolveGMRES: the algorithm of bfSolveGMRES (src/linalg.c:47) with the Krylov basis
+        resident in HBM.  Returns (x, num_iter, rel_residual, num_applies)."""
+        b = np.ascontiguousarray(b, dtype=np.complex128).reshape(-1)
+        x0a = None if x0 is None else np.ascontiguousarray(x0, dtype=np.complex128).reshape(-1)
+        x = np.empty_like(b)
+        it, res, na = C.c_int64(), C.c_double(), C.c_int64()
+        capi.check(
+            self.lib.bfCudaSolveGMRES(self.handle, b.ctypes.data, None if x0a is None else x0a.ctypes.data, float(tol), int(max_iter),
+                                      x.ctypes.data, C.byref(it), C.byref(res), C.byref(na)),
+            "bfCudaSolveGMRES",
+        )
+        return x, it.value, res.value, na.value
+
     def apply_device(self, x, y, op: int = capi.OP_N, stream=None):
         """y = op(A) x on torch CUDA tensors (row-major n x nrhs, last stride 1).  Asynchronous."""
         assert x.is_cuda and y.is_cuda and x.stride(-1) == 1 and y.stride(-1) == 1

@@ -179,6 +179,20 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *plan, int32_t op, const void *d_x, in
 BfCudaStatus bfCudaApplyHost(BfCudaPlan *plan, int32_t op, const void *x, int64_t ldx,
                              int64_t nrhs, void *y, int64_t ldy);
 
+/* The plan's own CUDA stream (a cudaStream_t as void*): what a NULL `stream` argument means. */
+void *bfCudaPlanGetStream(const BfCudaPlan *plan);
+
+/* Device-resident GMRES around the apply: solves A x = b for ONE complex right-hand side with the
+ * algorithm of bfSolveGMRES (src/linalg.c:47-318) — modified Gram-Schmidt Arnoldi, the reference's
+ * Givens rotations (src/vec_complex.c:155-168,230-290), convergence when |s[j+1]| / ||r0|| < tol,
+ * and, like the reference, the iterate rebuilt from the first *numIter basis vectors (the column on
+ * which the test fires is not counted, src/linalg.c:224-238).  No preconditioner.  b, x0 (may be
+ * NULL = zero) and x are host arrays of numRows complex doubles; the Krylov basis stays in HBM.
+ * relResidual (may be NULL) receives the last |s[j+1]| / ||r0||, numApplies the operator applies. */
+BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, double tol,
+                              int64_t maxNumIter, void *x, int64_t *numIter, double *relResidual,
+                              int64_t *numApplies);
+
 /* Number of kernel launches the last apply on this plan issued (bench.py's gpu_launches). */
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *plan);
 

@@ -265,3 +265,37 @@ BfMat *refStreamGetMat(RefStream *s) {
   return s->Phi;
 }
 int64_t refStreamNumFreqs(RefStream *s) { return (int64_t)s->freqs->size; }
+
+/* ---- second-kind system + GMRES (examples/multiple_scattering/multiple_scattering_context.c:456-487) */
+#include <bf/mat_diag_real.h>
+
+/* K <- K diag(w) + I/2 on the multilevel butterfly: bfMatScaleCols with constant trapezoid weights
+ * and bfMatAddInplace with bfMatDiagRealNewConstant(n, n, 0.5), exactly as the example does. */
+void refHelm2MakeSecondKind(RefHelm2 *h, double weight) {
+  BfSize n = bfMatGetNumRows(h->A);
+  BfVecReal *w = bfVecRealNewEmpty(n);
+  for (BfSize i = 0; i < n; ++i) w->data[i] = weight;
+  bfMatScaleCols(h->A, bfVecRealToVec(w));
+  BfVec *wv = bfVecRealToVec(w);
+  bfVecDelete(&wv);
+  BfMat *oneHalfEye = bfMatDiagRealToMat(bfMatDiagRealNewConstant(n, n, 0.5));
+  bfMatAddInplace(h->A, oneHalfEye);
+  bfMatDelete(&oneHalfEye);
+}
+
+/* X = bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, NULL) (src/linalg.c:47), B n x 1 complex.
+ * Returns seconds; writes the iteration count. */
+double refSolveGMRES(BfMat const *A, const double *b, int64_t n, double tol, int64_t maxNumIter, double *x, int64_t *numIter) {
+  BfMatDenseComplex *B = bfMatDenseComplexNewViewFromPtr((BfSize)n, 1, (BfComplex *)b);
+  BfSize it = 0;
+  double t0 = refNow();
+  BfMat *X = bfSolveGMRES(A, bfMatDenseComplexToMat(B), NULL, tol, (BfSize)maxNumIter, &it, NULL);
+  double t1 = refNow();
+  BfMatDenseComplex *Xd = bfMatToMatDenseComplex(X);
+  for (int64_t i = 0; i < n; ++i) memcpy(x + 2 * i, Xd->data + i * Xd->rowStride, sizeof(BfComplex));
+  bfMatDelete(&X);
+  BfMat *Bm = bfMatDenseComplexToMat(B);
+  bfMatDelete(&Bm);
+  *numIter = (int64_t)it;
+  return t1 - t0;
+}

@@ -53,6 +53,8 @@ def load():
         d.refRealRandn.argtypes = [i64, vp]; d.refRealRandn.restype = None
         d.refOpenblasThreads.argtypes = [C.c_int]; d.refOpenblasThreads.restype = C.c_int
         d.refPrintBlocks.argtypes = [vp, C.c_char_p]; d.refPrintBlocks.restype = None
+        d.refHelm2MakeSecondKind.argtypes = [vp, dbl]; d.refHelm2MakeSecondKind.restype = None
+        d.refSolveGMRES.argtypes = [vp, vp, i64, dbl, i64, vp, vp]; d.refSolveGMRES.restype = dbl
         _drv = d
     return _drv
 
@@ -118,6 +120,21 @@ class Helm2:
         y = np.zeros((self.drv.refMatNumRows(self.mat), x.shape[1]), np.complex128)
         t = self.drv.refMatMulComplex(self.mat, x.ctypes.data, x.shape[0], x.shape[1], y.ctypes.data)
         return y, t
+
+    def make_second_kind(self, weight: float | None = None):
+        """K <- K diag(w) + I/2 with the reference's own bfMatScaleCols / bfMatAddInplace
+        (examples/multiple_scattering/multiple_scattering_context.c:456-487); w = trapezoid weight
+        2 pi / n of the unit circle by default."""
+        self.drv.refHelm2MakeSecondKind(self.h, float(2 * np.pi / self.n if weight is None else weight))
+
+    def solve_gmres(self, b: np.ndarray, tol: float = 1e-12, max_iter: int = 50):
+        """bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, NULL) (src/linalg.c:47) through the
+        object's CURRENT vtable.  Returns (x, num_iter, seconds)."""
+        b = np.ascontiguousarray(b, dtype=np.complex128).reshape(-1)
+        x = np.zeros_like(b)
+        it = C.c_int64()
+        t = self.drv.refSolveGMRES(self.mat, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
+        return x, it.value, t
 
     def flatten(self) -> RawOps:
         a = load_attach()
