@@ -133,6 +133,8 @@ class DebugTables(C.Structure):
         ("tileCol0", C.POINTER(C.c_int32)),
         ("pool16", C.c_uint64),
         ("pool", C.c_void_p),
+        ("wsArena0Rows", C.c_int64),
+        ("wsArena1Rows", C.c_int64),
         ("owner", C.c_void_p),
     ]
 
@@ -158,6 +160,9 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanLastLaunchCount",
     "bfCudaMeasureFp64Peak",
     "bfCudaPlanGetStream",
+    "bfCudaApplyStages",
+    "bfCudaPlanGetWorkspace",
+    "bfCudaPlanGetWorkspaceLayout",
     "bfCudaSolveGMRES",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
@@ -244,6 +249,12 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaLastErrorMessage.restype = C.c_char_p
     lib.bfCudaMeasureFp64Peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.bfCudaMeasureFp64Peak.restype = i32
+    lib.bfCudaApplyStages.argtypes = [vp, i32, vp, i64, i64, vp, i64, i64, i64, vp]
+    lib.bfCudaApplyStages.restype = i32
+    lib.bfCudaPlanGetWorkspace.argtypes = [vp, i32, i64, C.POINTER(vp), C.POINTER(i64)]
+    lib.bfCudaPlanGetWorkspace.restype = i32
+    lib.bfCudaPlanGetWorkspaceLayout.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
+    lib.bfCudaPlanGetWorkspaceLayout.restype = i32
     lib.bfCudaPlanGetStream.argtypes = [vp]
     lib.bfCudaPlanGetStream.restype = vp
     lib.bfCudaSolveGMRES.argtypes = [vp, vp, vp, C.c_double, i64, vp, C.POINTER(i64), C.POINTER(C.c_double), C.POINTER(i64)]

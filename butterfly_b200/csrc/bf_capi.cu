@@ -294,8 +294,10 @@ static BfCudaStatus ensureBytes(unsigned char **p, size_t *have, size_t want) {
   return BF_CUDA_OK;
 }
 
-BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs,
-                               void *d_y, int64_t ldy, void *streamOpaque) {
+// Stages [sBegin, sEnd) of one apply; sEnd < 0 = all.  staged = a stage range was requested: the
+// RHS block must then fit one workspace chunk so that the workspace persists between calls.
+static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs, void *d_y,
+                              int64_t ldy, void *streamOpaque, int64_t sBegin, int64_t sEnd, bool staged) {
   if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
   if (op < 0 || op > 2 || !P->dir[op].built) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "direction not built (set buildTranspose)");
   if (nrhs < 0 || (nrhs > 0 && (ldx < nrhs || ldy < nrhs))) return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "ldx / ldy smaller than nrhs");
@@ -328,6 +330,9 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
   }
   const size_t nS = D.stages.size();
   const size_t Q = (size_t)D.numQueues;
+  if (sEnd < 0) sEnd = (int64_t)nS;
+  if (sBegin < 0 || sEnd > (int64_t)nS || sBegin > sEnd) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "stage range");
+  if (staged && chunk != nrhs) return fail(BF_CUDA_ERROR_NOT_IMPLEMENTED, "stage-by-stage apply needs the RHS block to fit one workspace chunk");
   if (P->profiling) {
     while (P->events.size() < nS + 1) { cudaEvent_t e; BF_CUDA_TRY(cudaEventCreate(&e)); P->events.push_back(e); }
   }
@@ -345,7 +350,9 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
     // The 1-RHS kernel bulk-copies operand segments: they must be dense and 16-byte aligned (real
     // segments may start 8 bytes into a 16-byte window, so they always go through the padded copy).
     const bool needStage = scatterIn != nullptr || (cplx && (reinterpret_cast<uintptr_t>(xp) & 15)) || (nc == 1 && (!cplx || ldx != 1));
-    if (needStage) {
+    if (needStage && sBegin > 0) {
+      a.base[kSpaceX] = P->scratch + wsBytes; a.ld[kSpaceX] = nc; // staged by the call that ran stage 0
+    } else if (needStage) {
       unsigned char *xs = P->scratch + wsBytes;
       cudaError_t e = launchPermuteRows(reinterpret_cast<const double *>(xp), ldx, reinterpret_cast<double *>(xs), nc,
                                         scatterIn, D.rowsIn, (int)nc, ed, stream);
@@ -355,7 +362,7 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
     } else {
       a.base[kSpaceX] = const_cast<unsigned char *>(xp); a.ld[kSpaceX] = ldx;
     }
-    for (size_t s = 0; s < nS; ++s) {
+    for (size_t s = (size_t)sBegin; s < (size_t)sEnd; ++s) {
       if (P->profiling && c0 == 0) BF_CUDA_TRY(cudaEventRecord(P->events[s], stream));
       a.items = dd.items + dd.itemOff[s];
       a.tiles = dd.tiles + dd.tileOff[s];
@@ -366,10 +373,48 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64
       if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("stage launch: ") + cudaGetErrorString(e));
       ++launches;
     }
-    if (P->profiling && c0 == 0) BF_CUDA_TRY(cudaEventRecord(P->events[nS], stream));
+    if (P->profiling && c0 == 0 && sEnd == (int64_t)nS) BF_CUDA_TRY(cudaEventRecord(P->events[nS], stream));
   }
   P->lastStages = (int64_t)nS;
   P->lastLaunches = launches;
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaApplyDevice(BfCudaPlan *P, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs,
+                               void *d_y, int64_t ldy, void *streamOpaque) {
+  return applyImpl(P, op, d_x, ldx, nrhs, d_y, ldy, streamOpaque, 0, -1, false);
+}
+
+BfCudaStatus bfCudaApplyStages(BfCudaPlan *P, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs, void *d_y,
+                               int64_t ldy, int64_t stageBegin, int64_t stageEnd, void *streamOpaque) {
+  return applyImpl(P, op, d_x, ldx, nrhs, d_y, ldy, streamOpaque, stageBegin, stageEnd, true);
+}
+
+BfCudaStatus bfCudaPlanGetWorkspaceLayout(const BfCudaPlan *P, int32_t op, int64_t *a0, int64_t *a1, int64_t *ded) {
+  if (!P || op < 0 || op > 2 || !P->dir[op].built) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "direction not built");
+  const Direction &D = P->dir[op].host;
+  if (a0) *a0 = D.wsArena[0];
+  if (a1) *a1 = D.wsArena[1];
+  if (ded) *ded = D.wsRows - D.wsArena[0] - D.wsArena[1];
+  return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaPlanGetWorkspace(BfCudaPlan *P, int32_t op, int64_t nrhs, void **d_ws, int64_t *ld) {
+  if (!P || op < 0 || op > 2 || !P->dir[op].built || nrhs <= 0 || !d_ws) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "bad argument");
+  DeviceGuard g(P->device);
+  const Direction &D = P->dir[op].host;
+  const size_t es = P->dtype == BF_CUDA_COMPLEX_F64 ? 16 : 8;
+  const size_t rowsPad = (size_t)D.wsRows + 2, xRowsPad = (size_t)D.rowsIn + 2;
+  if ((rowsPad + xRowsPad) * (size_t)nrhs * es > P->maxScratchBytes) return fail(BF_CUDA_ERROR_NOT_IMPLEMENTED, "RHS block does not fit one workspace chunk");
+  const size_t wsBytes = ((rowsPad * (size_t)nrhs * es + 255) / 256) * 256;
+  const size_t need = wsBytes + xRowsPad * (size_t)nrhs * es + 256;
+  if (P->scratchBytes < need) {
+    BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
+    BfCudaStatus st = ensureBytes(&P->scratch, &P->scratchBytes, need);
+    if (st != BF_CUDA_OK) return st;
+  }
+  *d_ws = P->scratch;
+  if (ld) *ld = nrhs;
   return BF_CUDA_OK;
 }
 

@@ -63,6 +63,7 @@ extern "C" BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t o
   t.qItemBegin = o->qItemBegin.data(); t.qTileBegin = o->qTileBegin.data(); t.qPool16 = o->qPool16.data();
   t.tileOp = o->tileOp.data(); t.tileRow0 = o->tileRow0.data(); t.tileCol0 = o->tileCol0.data();
   t.pool16 = D.pool16; t.pool = o->pool.data();
+  t.wsArena0Rows = D.wsArena[0]; t.wsArena1Rows = D.wsArena[1];
   t.owner = o;
   *out = &t;
   return BF_CUDA_OK;

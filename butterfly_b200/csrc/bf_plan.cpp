@@ -74,6 +74,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     if (o.m == 0 || o.k == 0) continue;
     DirOp d{};
     d.kind = o.kind;
+    d.remote = (o.flags & BF_CUDA_LEAF_REMOTE) ? 1 : 0;
     d.rawIndex = ri;
     d.val = o.val;
     d.ld = o.ld;
@@ -109,7 +110,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     firstW[d.outBuf] = std::min(firstW[d.outBuf], d.stage);
     lastW[d.outBuf] = std::max(lastW[d.outBuf], d.stage);
     numStages = std::max(numStages, d.stage + 1);
-    if (d.kind == BF_CUDA_LEAF_DENSE) D.entries += d.m * d.k;
+    if (d.kind == BF_CUDA_LEAF_DENSE && !d.remote) D.entries += d.m * d.k;
   }
   for (const DirOp &d : D.ops)
     if (d.inBuf != D.inBufId && lastW[d.inBuf] < 0) {
@@ -151,6 +152,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
       else if (cls[b] == 2) D.wsOffset[b] = arena[0] + arena[1] + off[b];
     }
     D.wsRows = arena[0] + arena[1] + dedicated;
+    D.wsArena[0] = arena[0]; D.wsArena[1] = arena[1];
     if (D.wsRows > (int64_t)kRowMask || D.rowsIn > (int64_t)kRowMask || D.rowsOut > (int64_t)kRowMask) {
       err = "operator too large for 30-bit row addresses"; return BF_CUDA_ERROR_NOT_IMPLEMENTED;
     }
@@ -176,6 +178,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     return a < b;
   });
   std::vector<Elem> elems;
+  std::vector<uint8_t> remoteCovered; // per elem
   std::vector<Frag> frags;
   frags.reserve((size_t)nD + 16);
   std::vector<int64_t> bps;
@@ -209,13 +212,18 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
         const int64_t lo = std::lower_bound(bps.begin(), bps.end(), d.outOff) - bps.begin();
         const int64_t hi = std::lower_bound(bps.begin(), bps.end(), d.outOff + d.m) - bps.begin();
         for (int64_t e = lo; e < hi; ++e) {
+          if (d.remote) { // another rank produces these rows: no items here, and not a hole either
+            if ((int64_t)remoteCovered.size() <= e0 + e) remoteCovered.resize((size_t)(e0 + e) + 1, 0);
+            remoteCovered[(size_t)(e0 + e)] = 1;
+            continue;
+          }
           frags.push_back(Frag{d.stage, e0 + e, byOut[i]});
           elems[(size_t)(e0 + e)].minStage = std::min(elems[(size_t)(e0 + e)].minStage, d.stage);
         }
       }
       const int64_t e1 = (int64_t)elems.size();
       for (int64_t e = e0; e < e1; ++e)
-        if (elems[(size_t)e].minStage == INT_MAX) { // hole between two leaves
+        if (elems[(size_t)e].minStage == INT_MAX && !((int64_t)remoteCovered.size() > e && remoteCovered[(size_t)e])) { // hole between two leaves
           elems[(size_t)e].minStage = firstW[buf];
           frags.push_back(Frag{firstW[buf], e, -1});
         }

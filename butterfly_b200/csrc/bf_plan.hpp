@@ -69,6 +69,7 @@ struct DirOp {
   int32_t kind;      // BfCudaLeafKind
   uint8_t swapRC;    // D(p,q) = stored(q,p) instead of stored(p,q)
   uint8_t conj;      // D takes the complex conjugate of the stored value
+  uint8_t remote;    // BF_CUDA_LEAF_REMOTE: part of the structure, applied by another rank
   int64_t rawIndex;  // index in the BfCudaPlanDesc op list (synthetic values hash on this)
   int64_t inBuf, inOff, outBuf, outOff, m, k;
   int64_t ld;        // stored row stride (elements)
@@ -99,6 +100,7 @@ struct Direction {
   std::vector<Stage> stages;
   std::vector<int64_t> wsOffset;      // per virtual buffer: first row in the workspace (-1: X / Y)
   int64_t wsRows = 0;                 // workspace rows per RHS column
+  int64_t wsArena[2] = {0, 0};        // rows of the two ping-pong arenas (the rest is dedicated)
   uint64_t pool16 = 0;                // total pool size, 16-byte units
   int64_t entries = 0;
   int64_t numItems = 0, numTiles = 0, maxTileK = 0, maxItemRows = 0;

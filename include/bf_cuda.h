@@ -85,6 +85,11 @@ typedef enum BfCudaLeafKind {
  * bit set acts as the CONJUGATE transpose. */
 #define BF_CUDA_LEAF_TRANS 2u
 #define BF_CUDA_LEAF_CONJ 4u
+/* Block-row sharding: the leaf belongs to the operator's structure — stages,
+ * workspace layout and row addresses are computed from ALL leaves, identically on every rank — but
+ * another rank applies it: no items, tiles or pool bytes are generated for it here, and the rows it
+ * writes are expected to arrive through the caller's exchange (bfCudaApplyStages). */
+#define BF_CUDA_LEAF_REMOTE 8u
 
 enum { BF_CUDA_BUF_X = 0, BF_CUDA_BUF_Y = 1, BF_CUDA_BUF_FIRST_TEMP = 2 };
 
@@ -173,6 +178,21 @@ BfCudaStatus bfCudaPlanSetPerms(BfCudaPlan *plan, const int64_t *inPerm, const i
  * cudaStream_t passed as void* (NULL = the plan's own stream).  Asynchronous w.r.t. the host. */
 BfCudaStatus bfCudaApplyDevice(BfCudaPlan *plan, int32_t op, const void *d_x, int64_t ldx,
                                int64_t nrhs, void *d_y, int64_t ldy, void *stream);
+
+/* Stage-by-stage apply for callers that interleave an exchange between stages (block-row sharding:
+ * every rank runs its own leaves of stage s, then rows of the workspace produced for other ranks
+ * are exchanged before stage s + 1).  Runs stages [stageBegin, stageEnd) of direction `op`; the
+ * operand is staged when stageBegin == 0.  nrhs must fit one workspace chunk (NOT_IMPLEMENTED
+ * otherwise).  bfCudaPlanGetWorkspace gives the device workspace those stages read and write: row r
+ * of the workspace starts at ws + r * ld * elemSize; valid until the next apply with a larger nrhs.
+ * bfCudaPlanGetWorkspaceLayout: rows [0, arena0) and [arena0, arena0 + arena1) are the two
+ * ping-pong arenas (a row written at stage t is read at stage t + 1 only), the remaining
+ * `dedicated` rows belong to buffers written over several stages and are never reused. */
+BfCudaStatus bfCudaApplyStages(BfCudaPlan *plan, int32_t op, const void *d_x, int64_t ldx, int64_t nrhs,
+                               void *d_y, int64_t ldy, int64_t stageBegin, int64_t stageEnd, void *stream);
+BfCudaStatus bfCudaPlanGetWorkspace(BfCudaPlan *plan, int32_t op, int64_t nrhs, void **d_ws, int64_t *ld);
+BfCudaStatus bfCudaPlanGetWorkspaceLayout(const BfCudaPlan *plan, int32_t op, int64_t *arena0Rows,
+                                          int64_t *arena1Rows, int64_t *dedicatedRows);
 
 /* Host-buffer apply: H2D of X, apply, D2H of Y, synchronous.  x / y are ordinary host memory
  * (the reference's malloc'ed BfMatDenseComplex::data / BfVecReal::data). */

@@ -32,6 +32,7 @@ typedef struct BfCudaDebugTables {
   const int32_t *tileCol0;
   uint64_t pool16;               /* pool size in 16-byte units */
   const void *pool;              /* packed values (zeros where val == NULL) */
+  int64_t wsArena0Rows, wsArena1Rows; /* ping-pong arenas; rows past them are dedicated (bf_cuda.h) */
   void *owner;                   /* opaque */
 } BfCudaDebugTables;
 

@@ -34,52 +34,62 @@ class Tables:
         self.num_stages, self.num_queues = nS, Q
         self.rows_in, self.rows_out, self.ws_rows = d.rowsIn, d.rowsOut, d.wsRows
         self.cplx = d.dtype == capi.COMPLEX_F64
+        self.ws_arena = (int(d.wsArena0Rows), int(d.wsArena1Rows))
 
     def close(self):
         if self._t:
             self.lib.bfCudaDebugFree(self._t)
             self._t = None
 
-    def apply(self, x):
+    def new_space(self, x):
+        """[X, Y, workspace] with everything but X NaN-initialised."""
         dt = np.complex128 if self.cplx else np.float64
         x = np.asarray(x, dtype=dt)
         if x.ndim == 1:
             x = x[:, None]
         nrhs = x.shape[1]
         nan = np.nan * (1 + 1j) if self.cplx else np.nan
-        space = [x, np.full((self.rows_out, nrhs), nan, dt), np.full((self.ws_rows + 2, nrhs), nan, dt)]
+        return [x, np.full((self.rows_out, nrhs), nan, dt), np.full((self.ws_rows + 2, nrhs), nan, dt)]
+
+    def run_stage(self, space, s):
+        dt = space[1].dtype
+        nrhs = space[0].shape[1]
         e = 2 if self.cplx else 1
-        for s in range(self.num_stages):
-            i0, i1 = self.stage_item[s], self.stage_item[s + 1]
-            t0 = self.stage_tile[s]
-            # an item's reads see the state before this stage (no intra-stage dependencies allowed)
-            results = []
-            for it in self.items[i0:i1]:
-                rows = int(it["rows"])
-                acc = np.zeros((rows, nrhs), dt)
-                for t in range(t0 + int(it["tileBegin"]), t0 + int(it["tileBegin"]) + int(it["numTiles"])):
-                    tl = self.tiles[t]
-                    assert int(tl["rows"]) == rows
-                    sp, r = int(tl["inAddr"]) >> 30, int(tl["inAddr"]) & capi.ROW_MASK
-                    kc = int(tl["kc"])
-                    p0 = int(self.tile_pool16[t]) * 2
-                    if kc == capi.KC_IDENTITY:
-                        acc += space[sp][r:r + rows]
-                    elif kc == capi.KC_DIAG:
-                        acc += self.pool[p0:p0 + rows, None] * space[sp][r:r + rows]
-                    else:
-                        a = self.pool[p0:p0 + rows * kc * e]
-                        a = a.view(np.complex128) if self.cplx else a
-                        acc += a.reshape(rows, kc) @ space[sp][r:r + kc]
-                results.append(acc)
-            for it, acc in zip(self.items[i0:i1], results):
-                sp, r = int(it["outAddr"]) >> 30, int(it["outAddr"]) & capi.ROW_MASK
-                assert sp != capi.SPACE_X
-                rows = int(it["rows"])
-                if int(it["flags"]) & capi.ITEM_ACCUMULATE:
-                    space[sp][r:r + rows] += acc
+        i0, i1 = self.stage_item[s], self.stage_item[s + 1]
+        t0 = self.stage_tile[s]
+        # an item's reads see the state before this stage (no intra-stage dependencies allowed)
+        results = []
+        for it in self.items[i0:i1]:
+            rows = int(it["rows"])
+            acc = np.zeros((rows, nrhs), dt)
+            for t in range(t0 + int(it["tileBegin"]), t0 + int(it["tileBegin"]) + int(it["numTiles"])):
+                tl = self.tiles[t]
+                assert int(tl["rows"]) == rows
+                sp, r = int(tl["inAddr"]) >> 30, int(tl["inAddr"]) & capi.ROW_MASK
+                kc = int(tl["kc"])
+                p0 = int(self.tile_pool16[t]) * 2
+                if kc == capi.KC_IDENTITY:
+                    acc += space[sp][r:r + rows]
+                elif kc == capi.KC_DIAG:
+                    acc += self.pool[p0:p0 + rows, None] * space[sp][r:r + rows]
                 else:
-                    space[sp][r:r + rows] = acc
+                    a = self.pool[p0:p0 + rows * kc * e]
+                    a = a.view(np.complex128) if self.cplx else a
+                    acc += a.reshape(rows, kc) @ space[sp][r:r + kc]
+            results.append(acc)
+        for it, acc in zip(self.items[i0:i1], results):
+            sp, r = int(it["outAddr"]) >> 30, int(it["outAddr"]) & capi.ROW_MASK
+            assert sp != capi.SPACE_X
+            rows = int(it["rows"])
+            if int(it["flags"]) & capi.ITEM_ACCUMULATE:
+                space[sp][r:r + rows] += acc
+            else:
+                space[sp][r:r + rows] = acc
+
+    def apply(self, x):
+        space = self.new_space(x)
+        for s in range(self.num_stages):
+            self.run_stage(space, s)
         return space[1]
 
     def check_queues(self):

@@ -1,0 +1,129 @@
+"""CPU, gloo, world_size 2 (and 3): block-row sharding (butterfly_b200/rowshard.py).
+Each rank compiles the operator with the other ranks' leaves flagged REMOTE, runs its stages with the
+table interpreter (NaN-initialised workspace: a row that was neither produced locally nor exchanged
+poisons the result), exchanges workspace rows through all_to_all_single after every stage, and the
+gathered Y must equal the unsharded oracle apply."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class InterpBackend:
+    """Stage runner over tests/table_interp.Tables (stands in for bfCudaApplyStages)."""
+
+    def __init__(self, raw_local):
+        from table_interp import Tables
+
+        self.T = Tables(raw_local, num_queues=148 * 12)
+
+    def begin(self, x, y):
+        import torch
+
+        self.space = self.T.new_space(x.numpy())
+        self.y = y
+        return torch.from_numpy(self.space[2])  # shares memory with the interpreter's workspace
+
+    def run_stage(self, t):
+        self.T.run_stage(self.space, t)
+
+    def end(self):
+        import torch
+
+        self.y.copy_(torch.from_numpy(self.space[1]))
+
+
+def _worker(rank, world, port, case, nrhs, q):
+    try:
+        sys.path.insert(0, str(ROOT))
+        sys.path.insert(0, str(ROOT / "tests"))
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch
+        import torch.distributed as dist
+
+        from butterfly_b200 import capi, rowshard, synth
+        from butterfly_b200.rawops import RawOps
+        from oracle import portlib
+
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        if case == "hodbf":
+            raw = synth.random_hodbf(n=1536, dtype=capi.COMPLEX_F64, seed=3, exotic=True)
+        elif case == "real":
+            raw = synth.lbo_like(num_rows=3000, num_eigs=256, bands=4, depth=3, rank_lo=5, rank_hi=12, with_values=True)
+        else:
+            raw = RawOps.load(ROOT / "tests" / "golden" / "lbo_stream_n600.npz")
+        cplx = raw.dtype == capi.COMPLEX_F64
+        rng = np.random.default_rng(11)
+        x = rng.standard_normal((raw.num_cols, nrhs)) + (1j * rng.standard_normal((raw.num_cols, nrhs)) if cplx else 0)
+        op = rowshard.RowShardedOperator(raw, world, rank, InterpBackend)
+        xt = torch.from_numpy(np.ascontiguousarray(x))
+        y = torch.full((raw.num_rows, nrhs), float("nan"), dtype=xt.dtype)
+        op.apply(xt, y)
+        r0, r1 = op.y_range
+        y_ref = portlib.apply(raw, x, capi.OP_N)
+        own_ok = bool(np.linalg.norm(y.numpy()[r0:r1] - y_ref[r0:r1]) <= 1e-12 * np.linalg.norm(y_ref))
+        full = op.gather_rows(y).numpy()
+        err = float(np.linalg.norm(full - y_ref) / np.linalg.norm(y_ref))
+        total_e = None
+        es = [None] * world
+        dist.all_gather_object(es, op.local_entries)
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, own_ok, err, (r0, r1), op.exchanged_rows, es, raw.num_entries, sum(op.stage_exchanges)))
+    except Exception as e:  # pragma: no cover
+        import traceback
+
+        q.put((rank, False, repr(e) + traceback.format_exc()[-1500:], None, 0, [], 0, 0))
+
+
+@pytest.mark.parametrize("case,world,nrhs", [("hodbf", 2, 1), ("hodbf", 3, 2), ("real", 2, 1), ("stream_golden", 2, 1)])
+def test_block_row_sharding(case, world, nrhs):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, case, nrhs, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    for rank, own_ok, err, rng_, exch, es, total, nex in res:
+        assert own_ok, (rank, err)
+        assert isinstance(err, float) and err <= 1e-12, (rank, err)
+    # the Y ranges tile [0, n) and the leaves are partitioned: local entries add up to E
+    spans = [r[3] for r in res]
+    assert spans[0][0] == 0 and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    assert sum(res[0][5]) == res[0][6]
+    if case == "hodbf":
+        assert max(res[0][5]) <= 0.75 * res[0][6], "work is spread over the ranks"
+        if world == 3:
+            # with 2 ranks every off-diagonal butterfly of the HODLR targets one half: chains stay on one
+            # rank and nothing moves; 3 ranks cut through the top-level butterflies
+            assert any(r[4] > 0 for r in res) and res[0][7] > 0, "a chain spans ranks: rows must be exchanged"
+
+
+def test_owner_assignment_is_a_partition():
+    sys.path.insert(0, str(ROOT))
+    from butterfly_b200 import capi, rowshard, synth
+
+    raw0 = synth.random_hodbf(n=4096, dtype=capi.COMPLEX_F64, seed=1, exotic=True)
+    for world in (1, 2, 3, 4, 8):
+        raw, owner, cuts = rowshard.shard(raw0, world)
+        assert owner.min() >= 0 and owner.max() < world and len(cuts) == world + 1
+        assert cuts[0] == 0 and cuts[-1] == raw.num_rows and all(a <= b for a, b in zip(cuts, cuts[1:]))
+        wy = raw.ops["outBuf"] == 1
+        for i in np.nonzero(wy)[0]:  # a leaf writing Y lies inside its owner's range
+            assert cuts[owner[i]] <= raw.ops["outOff"][i] and raw.ops["outOff"][i] + raw.ops["m"][i] <= cuts[owner[i] + 1]
