@@ -33,9 +33,12 @@ def parse():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=int(os.environ.get("BF_BENCH_N", DEFAULT_N)))
+    ap.add_argument("--n", "--points", dest="n", type=int, default=int(os.environ.get("BF_BENCH_N", DEFAULT_N)))
     ap.add_argument("--k", type=float, default=0.0, help="wavenumber (default n / 40.96)")
     ap.add_argument("--nrhs", type=int, default=1, help="RHS columns PER GPU")
+    ap.add_argument("--shard", default="cols", choices=["cols", "rows"],
+                    help="cols: plan replicated, RHS columns sharded, no collective (default, weak scaling); "
+                         "rows: ONE operator block-row sharded over the ranks, workspace rows exchanged by all_to_all (strong scaling)")
     ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     return ap.parse_args()
@@ -149,6 +152,81 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
+    """Block-row sharded apply (SURVEY.md §8e / configs[4]): every rank holds 1 / world of the factors of
+    ONE operator, X is replicated, workspace rows that cross ranks move in one all_to_all_single per
+    stage.  Returns the result dict (rank 0) — strong scaling: the job is one apply of the operator."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from butterfly_b200 import capi, rowshard, workloads
+
+    n = n or args.n
+    steps, warmup = steps or args.steps, warmup or args.warmup
+    nrhs = args.nrhs
+    if world > 1 and rank != 0:
+        dist.barrier()
+    raw, meta = workloads.helm2_circle(n, None)
+    if world > 1 and rank == 0:
+        dist.barrier()
+    t0 = time.time()
+    op = rowshard.RowShardedOperator(raw, world, rank, lambda loc: rowshard.GpuBackend(loc, device=local_rank, synthetic_seed=2024))
+    build_s = time.time() - t0
+    E = int(raw.num_entries)
+    g = torch.Generator(device="cuda").manual_seed(1234)  # the operand is replicated: same seed everywhere
+    x = torch.randn(n, nrhs, dtype=torch.complex128, device="cuda", generator=g)
+    y = torch.zeros(n, nrhs, dtype=torch.complex128, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        op.apply(x, y)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        op.apply(x, y)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1) / steps
+    # end to end: pinned host operand in, own rows of the result out
+    xh = x.cpu().pin_memory()
+    r0, r1 = op.y_range
+    yh = torch.empty(max(r1 - r0, 1), nrhs, dtype=torch.complex128).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(steps, 10))
+    for _ in range(e2e_steps):
+        x.copy_(xh, non_blocking=True)
+        op.apply(x, y)
+        yh[: r1 - r0].copy_(y[r0:r1], non_blocking=True)
+        torch.cuda.synchronize()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    stats = torch.tensor([ms, e2e_s, float(op.local_entries), float(op.exchanged_rows)], device="cuda", dtype=torch.float64)
+    mx = stats.clone()
+    if world > 1:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    ms, e2e_s = float(mx[0]), float(mx[1])
+    res = {"workload": f"helm2_circle N={n} k={n / 40.96:g} nrhs={nrhs}, block-row sharded x{world}", "E": E,
+           "pool_GB_per_gpu_max": float(mx[2]) * 16 / 1e9, "ms_per_apply": ms, "gflops": 8.0 * E * nrhs / (ms * 1e-3) / 1e9,
+           "matvecs_per_s": nrhs / (ms * 1e-3), "gbs_aggregate": (16.0 * E + 32.0 * n * nrhs) / (ms * 1e-3) / 1e9,
+           "frac_of_aggregate_hbm_peak": (16.0 * E + 32.0 * n * nrhs) / (ms * 1e-3) / 1e9 / (peaks()[0] * world),
+           "load_imbalance_max_over_mean": float(mx[2]) / (float(stats[2]) / world), "exchanged_rows_per_apply": int(stats[3]),
+           "exchange_stages": int(sum(op.stage_exchanges)), "stages": op.num_stages, "build_s": round(build_s, 1),
+           "e2e_ms_per_apply": e2e_s * 1e3, "e2e_gflops": 8.0 * E * nrhs / e2e_s / 1e9,
+           "collective": "all_to_all_single (NCCL) per exchanging stage; X replicated; Y row-owned"}
+    op.backend.close()
+    del op, x, y
+    torch.cuda.empty_cache()
+    return res
+
+
 def run_ours(args, rank, local_rank, world):
     import numpy as np
     import torch
@@ -160,9 +238,32 @@ def run_ours(args, rank, local_rank, world):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    if world > 1:
+    if world > 1 or args.shard == "rows":
+        os.environ.setdefault("MASTER_PORT", "29533")
+        os.environ.setdefault("RANK", "0")
+        os.environ.setdefault("WORLD_SIZE", "1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n, nrhs = args.n, args.nrhs
+    if args.shard == "rows":
+        with ClockSampler(local_rank) as clk:
+            r = run_rows(args, rank, local_rank, world)
+        if rank == 0:
+            line = {"metric": "butterfly apply GFLOP/s (complex fp64, 1 RHS)" if nrhs == 1 else f"butterfly apply GFLOP/s (complex fp64, {nrhs} RHS)",
+                    "value": r["gflops"], "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                    "ms_per_step": r["ms_per_apply"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                    "dtype": "c128 (complex f64)", "data": "synthetic",
+                    "config": {"workload": r["workload"], "structure": "reference fac_helm2 (values synthetic)", "E": r["E"],
+                               "parallelism": f"block rows x{world} ({r['collective']})", "l2": "inputs larger than L2"},
+                    "matvecs_per_s": r["matvecs_per_s"], "clocks": clk.summary(),
+                    "e2e": {"value": r["e2e_gflops"], "unit": "GFLOP/s", "h2d_bytes_per_step": int(16 * n * nrhs), "d2h_bytes_per_step": int(16 * n * nrhs / world),
+                            "ms_per_step": r["e2e_ms_per_apply"], "api": "RowShardedOperator.apply (bfCudaApplyStages + all_to_all_single), pinned host buffers"},
+                    "gpu_launches": int(r["stages"] * args.steps),
+                    "roofline": {"bound": "hbm", "kernel": "bfGemvStage<complex>", "achieved": r["gbs_aggregate"] / world, "peak": peaks()[0], "unit": "GB/s",
+                                 "frac": r["frac_of_aggregate_hbm_peak"], "peak_source": peaks()[1], "traffic": None},
+                    "cpu_baseline": None, "row_shard": r}
+            print(json.dumps(line), flush=True)
+        dist.destroy_process_group()
+        return
     # structure: rank 0 of the node generates (cached on disk), the others wait and load it
     if world > 1 and rank != 0:
         dist.barrier()
@@ -321,6 +422,17 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:
             lbo = {"error": str(e)[:200]}
 
+    rows_extra = None
+    if not args.no_extra and nrhs == 1 and world > 1:
+        # side measurement, configs[4]: the SAME operator block-row sharded over the ranks (strong scaling)
+        plan.close()
+        del x, y
+        torch.cuda.empty_cache()
+        try:
+            rows_extra = run_rows(args, rank, local_rank, world, steps=min(args.steps, 20), warmup=3)
+        except Exception as e:
+            rows_extra = {"error": str(e)[:300]}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference_leg(steps=10, warmup=2)
@@ -346,9 +458,11 @@ def run_ours(args, rank, local_rank, world):
             "cpu_baseline": cpu,
             "rhs256": extra,
             "lbo_real": lbo,
+            "row_shard": rows_extra,
         }
         print(json.dumps(line), flush=True)
-    plan.close()
+    if rows_extra is None:
+        plan.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -49,8 +49,12 @@ extern "C" BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t o
   }
   o->stageItemBegin.push_back((int64_t)o->items.size());
   o->stageTileBegin.push_back((int64_t)o->tiles.size());
-  o->pool.assign((size_t)D.pool16 * 16 + 16, 0);
-  packPool(D, 0, D.stages.size(), o->pool.data());
+  bool anyVal = false; // value-less (structure-only) operators get tables without a packed pool
+  for (const DirOp &d : D.ops) if (d.val) { anyVal = true; break; }
+  if (anyVal) {
+    o->pool.assign((size_t)D.pool16 * 16 + 16, 0);
+    packPool(D, 0, D.stages.size(), o->pool.data());
+  }
   BfCudaDebugTables &t = o->t;
   std::memset(&t, 0, sizeof t);
   t.dtype = D.dtype; t.op = op;
@@ -62,7 +66,7 @@ extern "C" BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t o
   t.tilePool16 = o->tilePool16.data();
   t.qItemBegin = o->qItemBegin.data(); t.qTileBegin = o->qTileBegin.data(); t.qPool16 = o->qPool16.data();
   t.tileOp = o->tileOp.data(); t.tileRow0 = o->tileRow0.data(); t.tileCol0 = o->tileCol0.data();
-  t.pool16 = D.pool16; t.pool = o->pool.data();
+  t.pool16 = D.pool16; t.pool = anyVal ? o->pool.data() : nullptr;
   t.wsArena0Rows = D.wsArena[0]; t.wsArena1Rows = D.wsArena[1];
   t.owner = o;
   *out = &t;

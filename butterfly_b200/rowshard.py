@@ -74,57 +74,58 @@ def _cut_rows(starts, ends, rows_total, fractions):
 def assign_owners(raw: RawOps, y_cuts) -> np.ndarray:
     """owner[i] = rank that applies raw op i, given the Y row boundaries (no leaf writing Y may
     straddle one: shard() arranges that)."""
+    from scipy.sparse import coo_matrix
+    from scipy.sparse.csgraph import connected_components
+
     ops = raw.ops
     n_ops = raw.num_ops
     ib, ob = ops["inBuf"].astype(np.int64), ops["outBuf"].astype(np.int64)
     oo, m = ops["outOff"].astype(np.int64), ops["m"].astype(np.int64)
+    cuts = np.asarray(y_cuts, np.int64)
+    nparts = len(cuts) - 1
+    row_owner = lambda r: np.minimum(np.searchsorted(cuts, r, side="right") - 1, nparts - 1)
     owner = np.full(n_ops, -1, np.int64)
-    owner_of_row = lambda cuts, r: min(bisect.bisect_right(cuts, r) - 1, len(cuts) - 2)
 
-    # chains: connected components of intermediate buffers (union-find over ops touching temps)
+    # chains: connected components of intermediate buffers (a MatProduct's temporaries)
     nb = len(raw.buf_rows)
-    parent = np.arange(nb)
+    both = (ib >= 2) & (ob >= 2)
+    g = coo_matrix((np.ones(int(both.sum()), np.int8), (ib[both], ob[both])), shape=(nb, nb))
+    _, comp = connected_components(g, directed=False)
+    temp = np.where(ob >= 2, ob, np.where(ib >= 2, ib, -1))
+    chain = np.where(temp >= 0, comp[np.maximum(temp, 0)], -1)
+    direct = chain < 0
+    owner[direct] = row_owner(oo[direct])  # leaves that read X and write Y directly
 
-    def find(a):
-        while parent[a] != a:
-            parent[a] = parent[parent[a]]
-            a = parent[a]
-        return a
-
-    for i in range(n_ops):
-        a, b = ib[i], ob[i]
-        if a >= 2 and b >= 2:
-            ra, rb = find(a), find(b)
-            if ra != rb:
-                parent[rb] = ra
-    chain_of_op = np.full(n_ops, -1, np.int64)
-    for i in range(n_ops):
-        t = ob[i] if ob[i] >= 2 else (ib[i] if ib[i] >= 2 else -1)
-        if t >= 0:
-            chain_of_op[i] = find(t)
-    # leaves that read X and write Y directly: owner of their rows
-    for i in np.nonzero(chain_of_op < 0)[0]:
-        owner[i] = owner_of_row(y_cuts, oo[i])
-    for c in np.unique(chain_of_op[chain_of_op >= 0]):
-        idx = np.nonzero(chain_of_op == c)[0]
-        last = idx[ob[idx] == 1]
-        if len(last) == 0:  # a chain that never reaches Y (degenerate): rank 0
-            owner[idx] = 0
-            continue
-        r0, r1 = int(oo[last].min()), int((oo[last] + m[last]).max())
-        p0, p1 = owner_of_row(y_cuts, r0), owner_of_row(y_cuts, max(r1 - 1, r0))
-        if p0 == p1:
-            owner[idx] = p0
-            continue
-        ranks = list(range(p0, p1 + 1))
-        frac = np.array([max(min(y_cuts[p + 1], r1) - max(y_cuts[p], r0), 0) for p in ranks], np.float64)
-        for i in last:
-            owner[i] = owner_of_row(y_cuts, oo[i])
-        for b in np.unique(ob[idx][ob[idx] >= 2]):
-            w = idx[ob[idx] == b]
-            cuts = _cut_rows(oo[w], oo[w] + m[w], int(raw.buf_rows[b]), frac)
-            for i in w:
-                owner[i] = ranks[owner_of_row(cuts, oo[i])]
+    idx = np.nonzero(~direct)[0]
+    if len(idx) == 0:
+        return owner
+    order = idx[np.argsort(chain[idx], kind="stable")]
+    cid = chain[order]
+    starts = np.nonzero(np.concatenate([[True], cid[1:] != cid[:-1]]))[0]
+    ends = np.concatenate([starts[1:], [len(order)]])
+    # Y extent of every chain (leaves with outBuf == 1), vectorised
+    is_last = ob[order] == 1
+    big = np.iinfo(np.int64).max
+    lo = np.minimum.reduceat(np.where(is_last, oo[order], big), starts)
+    hi = np.maximum.reduceat(np.where(is_last, oo[order] + m[order], -1), starts)
+    never = hi < 0  # a chain that never reaches Y (degenerate): rank 0
+    p0 = np.where(never, 0, row_owner(np.where(never, 0, lo)))
+    p1 = np.where(never, 0, row_owner(np.maximum(np.where(never, 0, hi) - 1, np.where(never, 0, lo))))
+    chain_len = ends - starts
+    single = p0 == p1
+    owner[order] = np.repeat(np.where(single, p0, -1), chain_len)
+    for c in np.nonzero(~single)[0]:  # chains whose Y rows span ranks: cut every buffer proportionally
+        sel = order[starts[c]:ends[c]]
+        r0, r1 = int(lo[c]), int(hi[c])
+        ranks = list(range(int(p0[c]), int(p1[c]) + 1))
+        frac = np.array([max(min(int(cuts[p + 1]), r1) - max(int(cuts[p]), r0), 0) for p in ranks], np.float64)
+        last = sel[ob[sel] == 1]
+        owner[last] = row_owner(oo[last])
+        tsel = sel[ob[sel] >= 2]
+        for bb in np.unique(ob[tsel]):
+            w = tsel[ob[tsel] == bb]
+            bc = np.asarray(_cut_rows(oo[w], oo[w] + m[w], int(raw.buf_rows[bb]), frac), np.int64)
+            owner[w] = np.asarray(ranks)[np.minimum(np.searchsorted(bc, oo[w], side="right") - 1, len(ranks) - 1)]
     assert (owner >= 0).all()
     return owner
 
@@ -228,10 +229,11 @@ def _runs(mask: np.ndarray) -> np.ndarray:
 
 
 def _mask_from_runs(runs, n):
-    m = np.zeros(n, bool)
-    for a, b in runs:
-        m[a:b] = True
-    return m
+    d = np.zeros(n + 1, np.int8)
+    if len(runs):
+        d[runs[:, 0]] += 1
+        d[runs[:, 1]] -= 1  # runs are disjoint and sorted: the prefix sum is 0 / 1
+    return np.cumsum(d[:-1], dtype=np.int8).astype(bool)
 
 
 class StageTables:
@@ -281,34 +283,32 @@ def exchange_lists(all_have, all_need, ws_rows, arena, me: int):
     """For every stage t: (send_idx[q], recv_idx[p]) — workspace row indices this rank sends to q /
     receives from p after stage t, ascending (both sides derive the same lists).  A row produced at t
     in a ping-pong arena is wanted by the stage-(t+1) readers only; a dedicated row by any later
-    reader."""
+    reader.  Row ownership is disjoint, so a row src produced at t was not produced by dst."""
     world = len(all_have)
     nS = len(all_have[0])
     ded0 = arena[0] + arena[1]
-    have = [[_mask_from_runs(all_have[r][s], ws_rows) for s in range(nS)] for r in range(world)]
-    need = [[_mask_from_runs(all_need[r][s], ws_rows) for s in range(nS)] for r in range(world)]
+    nd = ws_rows - ded0
+    # dedicated rows needed at any stage > t, per rank (suffix OR), kept only for the dedicated tail
     later = [[None] * nS for _ in range(world)]
     for r in range(world):
-        acc = np.zeros(ws_rows, bool)
+        acc = np.zeros(nd, bool)
         for s in range(nS - 1, -1, -1):
-            later[r][s] = acc.copy()  # needed at any stage > s
-            acc |= need[r][s]
+            later[r][s] = acc.copy()
+            if nd:
+                acc |= _mask_from_runs(all_need[r][s], ws_rows)[ded0:]
     out = []
     for t in range(nS):
         send, recv = {}, {}
+        have_me = _mask_from_runs(all_have[me][t], ws_rows)
+        need_me = _mask_from_runs(all_need[me][t + 1], ws_rows) if t + 1 < nS else np.zeros(ws_rows, bool)
+        need_me[ded0:] = later[me][t]
         for q in range(world):
             if q == me:
                 continue
-
-            def wanted(dst, src):
-                w = np.zeros(ws_rows, bool)
-                if t + 1 < nS:
-                    w[:ded0] = need[dst][t + 1][:ded0]
-                w[ded0:] = later[dst][t][ded0:]
-                return have[src][t] & w  # row ownership is disjoint: dst did not produce these at t
-
-            s_idx = np.nonzero(wanted(q, me))[0]
-            r_idx = np.nonzero(wanted(me, q))[0]
+            want_q = _mask_from_runs(all_need[q][t + 1], ws_rows) if t + 1 < nS else np.zeros(ws_rows, bool)
+            want_q[ded0:] = later[q][t]
+            s_idx = np.nonzero(have_me & want_q)[0]
+            r_idx = np.nonzero(_mask_from_runs(all_have[q][t], ws_rows) & need_me)[0]
             if len(s_idx):
                 send[q] = s_idx
             if len(r_idx):

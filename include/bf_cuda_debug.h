@@ -31,7 +31,7 @@ typedef struct BfCudaDebugTables {
   const int32_t *tileRow0;       /* [numTiles] origin of the tile in the acting matrix */
   const int32_t *tileCol0;
   uint64_t pool16;               /* pool size in 16-byte units */
-  const void *pool;              /* packed values (zeros where val == NULL) */
+  const void *pool;              /* packed values (zeros where val == NULL); NULL if no op carries values */
   int64_t wsArena0Rows, wsArena1Rows; /* ping-pong arenas; rows past them are dedicated (bf_cuda.h) */
   void *owner;                   /* opaque */
 } BfCudaDebugTables;

@@ -30,7 +30,7 @@ class Tables:
         self.q_tile = arr(d.qTileBegin, nS * (Q + 1), np.uint32).reshape(nS, Q + 1)
         self.q_pool16 = arr(d.qPool16, nS * (Q + 1), np.uint64).reshape(nS, Q + 1)
         self.tile_op = arr(d.tileOp, d.numTiles, np.int64)
-        self.pool = arr(d.pool, int(d.pool16) * 2, np.float64)
+        self.pool = arr(d.pool, int(d.pool16) * 2, np.float64) if d.pool else np.zeros(0)
         self.num_stages, self.num_queues = nS, Q
         self.rows_in, self.rows_out, self.ws_rows = d.rowsIn, d.rowsOut, d.wsRows
         self.cplx = d.dtype == capi.COMPLEX_F64
