@@ -39,6 +39,9 @@ def parse():
     ap.add_argument("--shard", default="cols", choices=["cols", "rows"],
                     help="cols: plan replicated, RHS columns sharded, no collective (default, weak scaling); "
                          "rows: ONE operator block-row sharded over the ranks, workspace rows exchanged by all_to_all (strong scaling)")
+    ap.add_argument("--row-fractions", default="", help="--shard rows: comma-separated Y shares per rank (default equal); unequal shares cut "
+                                                         "through the top-level butterflies and exercise the exchange")
+    ap.add_argument("--verify", action="store_true", help="--shard rows: also apply the unsharded plan (must fit one GPU) and compare own rows")
     ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     return ap.parse_args()
@@ -171,7 +174,8 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
     if world > 1 and rank == 0:
         dist.barrier()
     t0 = time.time()
-    op = rowshard.RowShardedOperator(raw, world, rank, lambda loc: rowshard.GpuBackend(loc, device=local_rank, synthetic_seed=2024))
+    fr = [float(v) for v in args.row_fractions.split(",")] if args.row_fractions else None
+    op = rowshard.RowShardedOperator(raw, world, rank, lambda loc: rowshard.GpuBackend(loc, device=local_rank, synthetic_seed=2024), fractions=fr)
     build_s = time.time() - t0
     E = int(raw.num_entries)
     g = torch.Generator(device="cuda").manual_seed(1234)  # the operand is replicated: same seed everywhere
@@ -186,6 +190,20 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
     for _ in range(warmup):
         op.apply(x, y)
     barrier()
+    verify = None
+    if args.verify:
+        from butterfly_b200.plan import Plan
+
+        full = Plan(op.raw, device=local_rank)  # same leaves, same raw indices => same synthetic values
+        full.fill_synthetic(2024)
+        yf = torch.empty_like(y)
+        full.apply_device(x, yf, stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        r0v, r1v = op.y_range
+        verify = float((y[r0v:r1v] - yf[r0v:r1v]).norm() / yf[r0v:r1v].norm()) if r1v > r0v else 0.0
+        full.close()
+        del yf
+        torch.cuda.empty_cache()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(steps):
@@ -207,7 +225,7 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
         torch.cuda.synchronize()
     barrier()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
-    stats = torch.tensor([ms, e2e_s, float(op.local_entries), float(op.exchanged_rows)], device="cuda", dtype=torch.float64)
+    stats = torch.tensor([ms, e2e_s, float(op.local_entries), float(op.exchanged_rows), verify if verify is not None else -1.0], device="cuda", dtype=torch.float64)
     mx = stats.clone()
     if world > 1:
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -220,6 +238,7 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
            "load_imbalance_max_over_mean": float(mx[2]) / (float(stats[2]) / world), "exchanged_rows_per_apply": int(stats[3]),
            "exchange_stages": int(sum(op.stage_exchanges)), "stages": op.num_stages, "build_s": round(build_s, 1),
            "e2e_ms_per_apply": e2e_s * 1e3, "e2e_gflops": 8.0 * E * nrhs / e2e_s / 1e9,
+           "y_cuts": [int(c) for c in op.y_cuts], "verify_rel_l2_vs_unsharded_max": (float(mx[4]) if args.verify else None),
            "collective": "all_to_all_single (NCCL) per exchanging stage; X replicated; Y row-owned"}
     op.backend.close()
     del op, x, y

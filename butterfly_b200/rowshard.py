@@ -193,19 +193,19 @@ def split_diagonal_terms(raw: RawOps, y_cuts) -> RawOps:
     return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, np.array(out, dtype=ops.dtype), raw.values)
 
 
-def choose_y_cuts(raw: RawOps, world: int) -> List[int]:
-    """world + 1 row boundaries of Y: equal shares snapped to rows no DENSE leaf straddles."""
+def choose_y_cuts(raw: RawOps, world: int, fractions=None) -> List[int]:
+    """world + 1 row boundaries of Y: equal shares (or `fractions`) snapped to rows no DENSE leaf straddles."""
     ops = raw.ops
     wy = np.nonzero((ops["outBuf"] == 1) & (ops["kind"] == capi.LEAF_DENSE))[0]
     oo, m = ops["outOff"].astype(np.int64), ops["m"].astype(np.int64)
-    return _cut_rows(oo[wy], oo[wy] + m[wy], raw.num_rows, np.ones(world))
+    return _cut_rows(oo[wy], oo[wy] + m[wy], raw.num_rows, np.ones(world) if fractions is None else np.asarray(fractions, np.float64))
 
 
-def shard(raw: RawOps, world: int):
+def shard(raw: RawOps, world: int, fractions=None):
     """(raw', owner, y_cuts): the operator with tall / diagonal leaves cut at ownership boundaries, the
     rank that applies each of its leaves, and the Y row ranges."""
     raw = presplit_tall_leaves(raw)
-    y_cuts = choose_y_cuts(raw, world)
+    y_cuts = choose_y_cuts(raw, world, fractions)
     raw = split_diagonal_terms(raw, y_cuts)
     owner = assign_owners(raw, y_cuts)
     return raw, owner, y_cuts
@@ -323,12 +323,12 @@ class RowShardedOperator:
     workspace: GpuBackend (bfCudaApplyStages) in the product, the table interpreter in the CPU tests."""
 
     def __init__(self, raw: RawOps, world: int, rank: int, backend_factory, num_queues: int = 148 * 12, group=None,
-                 _pre=None):
+                 _pre=None, fractions=None):
         self.world, self.rank, self.group = world, rank, group
         if _pre is None:
             import torch.distributed as dist
 
-            raw, self.owner, self.y_cuts = shard(raw, world)
+            raw, self.owner, self.y_cuts = shard(raw, world, fractions)
             self.local = mask_for_rank(raw, self.owner, rank)
             st = StageTables(self.local, num_queues)
             gathered = [None] * world
@@ -353,10 +353,10 @@ class RowShardedOperator:
         self._idx_cache = {}
 
     @classmethod
-    def build_all_local(cls, raw: RawOps, world: int, backend_factory, num_queues: int = 148 * 12):
+    def build_all_local(cls, raw: RawOps, world: int, backend_factory, num_queues: int = 148 * 12, fractions=None):
         """All ranks' shares in ONE process, no process group: for emulating the sharded apply on a
         single device (emulate_apply)."""
-        raw2, owner, y_cuts = shard(raw, world)
+        raw2, owner, y_cuts = shard(raw, world, fractions)
         locs = [mask_for_rank(raw2, owner, r) for r in range(world)]
         sts = [StageTables(l, num_queues) for l in locs]
         gathered = [(s.have, s.need) for s in sts]
