@@ -41,6 +41,7 @@ def parse():
                          "rows: ONE operator block-row sharded over the ranks, workspace rows exchanged by all_to_all (strong scaling)")
     ap.add_argument("--row-fractions", default="", help="--shard rows: comma-separated Y shares per rank (default equal); unequal shares cut "
                                                          "through the top-level butterflies and exercise the exchange")
+    ap.add_argument("--solve", type=int, default=0, help="--shard rows: also time this many GMRES iterations over the sharded operator (configs[4])")
     ap.add_argument("--verify", action="store_true", help="--shard rows: also apply the unsharded plan (must fit one GPU) and compare own rows")
     ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -211,6 +212,21 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1) / steps
+    solve = None
+    if args.solve > 0 and nrhs == 1:
+        # configs[4]: repeated applies inside GMRES over the sharded operator.  Synthetic factor values do
+        # not make a convergent system, so a fixed number of iterations is timed (tol = 0).
+        from butterfly_b200 import gmres
+
+        bvec = x[:, 0].clone()
+        for orth in ("mgs", "cgs"):
+            barrier()
+            t0 = time.perf_counter()
+            _, its, resid, napp = gmres.solve_gmres_sharded(op, bvec, None, 0.0, args.solve, orth)
+            barrier()
+            dt = time.perf_counter() - t0
+            solve = dict(solve or {}, **{orth: {"iterations": int(its), "applies": int(napp), "ms_per_iteration": dt / max(its, 1) * 1e3,
+                                                "apply_share": ms * napp / (dt * 1e3)}})
     # end to end: pinned host operand in, own rows of the result out
     xh = x.cpu().pin_memory()
     r0, r1 = op.y_range
@@ -238,7 +254,7 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
            "load_imbalance_max_over_mean": float(mx[2]) / (float(stats[2]) / world), "exchanged_rows_per_apply": int(stats[3]),
            "exchange_stages": int(sum(op.stage_exchanges)), "stages": op.num_stages, "build_s": round(build_s, 1),
            "e2e_ms_per_apply": e2e_s * 1e3, "e2e_gflops": 8.0 * E * nrhs / e2e_s / 1e9,
-           "y_cuts": [int(c) for c in op.y_cuts], "verify_rel_l2_vs_unsharded_max": (float(mx[4]) if args.verify else None),
+           "gmres": solve, "y_cuts": [int(c) for c in op.y_cuts], "verify_rel_l2_vs_unsharded_max": (float(mx[4]) if args.verify else None),
            "collective": "all_to_all_single (NCCL) per exchanging stage; X replicated; Y row-owned"}
     op.backend.close()
     del op, x, y

@@ -188,3 +188,15 @@ def lbo_like(num_rows=500_000, num_eigs=4096, bands=16, depth=5, rank_lo=20, ran
     for j in range(bands):
         _butterfly(b, 0, (int(edges[j]), int(edges[j + 1])), 1, (0, num_rows), depth, rank_lo, rank_hi, False)
     return b.finish(num_rows, num_eigs)
+
+
+def shifted_identity_hodbf(n=1024, seed=5, scale=0.005) -> RawOps:
+    """I + (random exotic HODBF with its dense values scaled by `scale`): a well-conditioned complex
+    system for the GMRES tests (converges in a few dozen steps)."""
+    raw = random_hodbf(n=n, dtype=capi.COMPLEX_F64, seed=seed, exotic=True)
+    raw.values = raw.values * scale
+    ops = np.concatenate([raw.ops, np.zeros(1, raw.ops.dtype)])
+    o = ops[-1:]
+    o["kind"], o["flags"], o["inBuf"], o["inOff"], o["outBuf"], o["outOff"] = capi.LEAF_IDENTITY, 0, 0, 0, 1, 0
+    o["m"], o["k"], o["ld"], o["val"] = raw.num_rows, raw.num_cols, 0, 0
+    return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, ops, raw.values)

@@ -57,15 +57,38 @@ def test_device_gmres_on_synthetic_operator_with_initial_iterate():
 
 
 def portlib_safe_operator():
-    """I + (random HODBF scaled to norm ~1, incl. its identity block): GMRES converges in a few dozen steps."""
     from butterfly_b200 import synth
 
-    raw = synth.random_hodbf(n=1024, dtype=capi.COMPLEX_F64, seed=5, exotic=True)
-    raw.values = raw.values * 0.005
-    # the exotic variant already carries a real-diagonal leaf (values in [0.5, 1.5) * 0.02 now): add a plain identity
-    from butterfly_b200.rawops import RawOps
-    ops = np.concatenate([raw.ops, np.zeros(1, raw.ops.dtype)])
-    o = ops[-1:]
-    o["kind"], o["flags"], o["inBuf"], o["inOff"], o["outBuf"], o["outOff"] = capi.LEAF_IDENTITY, 0, 0, 0, 1, 0
-    o["m"], o["k"], o["ld"], o["val"] = raw.num_rows, raw.num_cols, 0, 0
-    return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, ops, raw.values)
+    return synth.shifted_identity_hodbf(1024, seed=5)
+
+
+def test_sharded_gmres_matches_device_gmres_world1():
+    """butterfly_b200/gmres.py (row-distributed GMRES; here one rank on one GPU, stage kernels through
+    bfCudaApplyStages) against bfCudaSolveGMRES on the same operator: same iteration count and iterate."""
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    from butterfly_b200 import gmres, rowshard
+
+    raw = portlib_safe_operator()
+    rng = np.random.default_rng(8)
+    n = raw.num_rows
+    b = rng.standard_normal(n) + 1j * rng.standard_normal(n)
+    with Plan(raw) as plan:
+        x_ref, it_ref, _, _ = plan.solve_gmres(b, None, 1e-12, 60)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29541")
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("gloo", rank=0, world_size=1)
+    try:
+        op = rowshard.RowShardedOperator(raw, 1, 0, rowshard.GpuBackend)
+        x, it, res, applies = gmres.solve_gmres_sharded(op, torch.from_numpy(b).cuda(), None, 1e-12, 60, "mgs")
+        assert it == it_ref
+        assert np.linalg.norm(x.cpu().numpy() - x_ref) / np.linalg.norm(x_ref) <= 1e-11
+        op.backend.close()
+    finally:
+        if created:
+            dist.destroy_process_group()
