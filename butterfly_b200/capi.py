@@ -159,6 +159,7 @@ EXPORTED_SYMBOLS = [
     "bfCudaApplyHost",
     "bfCudaPlanLastLaunchCount",
     "bfCudaMeasureFp64Peak",
+    "bfCudaMeasureFp64PeakSustained",
     "bfCudaPlanGetStream",
     "bfCudaApplyStages",
     "bfCudaPlanGetWorkspace",
@@ -249,6 +250,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaLastErrorMessage.restype = C.c_char_p
     lib.bfCudaMeasureFp64Peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.bfCudaMeasureFp64Peak.restype = i32
+    lib.bfCudaMeasureFp64PeakSustained.argtypes = [i32, C.c_double, C.POINTER(C.c_double)]
+    lib.bfCudaMeasureFp64PeakSustained.restype = i32
     lib.bfCudaApplyStages.argtypes = [vp, i32, vp, i64, i64, vp, i64, i64, i64, vp]
     lib.bfCudaApplyStages.restype = i32
     lib.bfCudaPlanGetWorkspace.argtypes = [vp, i32, i64, C.POINTER(vp), C.POINTER(i64)]

@@ -478,6 +478,40 @@ __device__ __forceinline__ void mbarArrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
+// One staged tile: C[mb][nb] += A(rows x kc) X(kc x 8 NB) for the first MBV row blocks.
+template <int NB, int MBV, int MB>
+__device__ __forceinline__ void mmaTile(double (&cr)[MB][NB][2], double (&ci)[MB][NB][2], const double2 *A,
+                                        const unsigned char *Xs, const uint32_t XS, const int rows, const int kc,
+                                        const int g, const int t4) {
+  constexpr int ES = 16;
+  const int ks = (kc + 3) >> 2;
+  int ra[MBV];
+#pragma unroll
+  for (int mb = 0; mb < MBV; ++mb) ra[mb] = min(mb * 8 + g, rows - 1) * kc;
+#pragma unroll 2
+  for (int s = 0; s < ks; ++s) {
+    const int k = s * 4 + t4;
+    const bool kOk = k < kc;
+    const int kcl = min(k, kc - 1);
+    double2 xb[NB], av[MBV];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) xb[nb] = *reinterpret_cast<const double2 *>(Xs + (uint32_t)kcl * XS + nb * (8 * ES));
+#pragma unroll
+    for (int mb = 0; mb < MBV; ++mb) {
+      av[mb] = A[ra[mb] + kcl];
+      if (!kOk) av[mb] = make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int mb = 0; mb < MBV; ++mb)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], av[mb].x, xb[nb].x); dmma884(ci[mb][nb], av[mb].x, xb[nb].y); }
+#pragma unroll
+    for (int mb = 0; mb < MBV; ++mb)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], -av[mb].y, xb[nb].y); dmma884(ci[mb][nb], av[mb].y, xb[nb].x); }
+  }
+}
+
 // work entry flags (word 0, above the 20-bit ring offset)
 constexpr uint32_t kEntFirst = 1u << 31, kEntLast = 1u << 30, kEntAccum = 1u << 29, kEntEnd = 1u << 28;
 constexpr uint32_t kEntOffMask = (1u << 20) - 1;
@@ -624,38 +658,15 @@ __global__ void __launch_bounds__(kMmaThreads) bfWideMmaStage(const __grid_const
         }
       } else {
         const int kc = (int)kcRaw;
-        const int ks = (kc + 3) >> 2;
         const double2 *A = reinterpret_cast<const double2 *>(T);
         const unsigned char *Xs = Xw + g * ES;
-        int ra[MB];
-#pragma unroll
-        for (int mb = 0; mb < MB; ++mb) ra[mb] = min(mb * 8 + g, rows - 1) * kc;
-        const int nmb = (rows + 7) >> 3;
-#pragma unroll 2
-        for (int s = 0; s < ks; ++s) {
-          const int k = s * 4 + t4;
-          const bool kOk = k < kc;
-          const int kcl = min(k, kc - 1);
-          double2 xb[NB], av[MB];
-#pragma unroll
-          for (int nb = 0; nb < NB; ++nb) xb[nb] = *reinterpret_cast<const double2 *>(Xs + (uint32_t)kcl * XS + nb * (8 * ES));
-#pragma unroll
-          for (int mb = 0; mb < MB; ++mb) {
-            av[mb] = A[ra[mb] + kcl];
-            if (!kOk) av[mb] = make_double2(0.0, 0.0);
-          }
-#pragma unroll
-          for (int mb = 0; mb < MB; ++mb)
-            if (mb < nmb) { // warp-uniform
-#pragma unroll
-              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], av[mb].x, xb[nb].x); dmma884(ci[mb][nb], av[mb].x, xb[nb].y); }
-            }
-#pragma unroll
-          for (int mb = 0; mb < MB; ++mb)
-            if (mb < nmb) {
-#pragma unroll
-              for (int nb = 0; nb < NB; ++nb) { dmma884(cr[mb][nb], -av[mb].y, xb[nb].y); dmma884(ci[mb][nb], av[mb].y, xb[nb].x); }
-            }
+        // exact fragment counts through a warp-uniform branch: a predicated-off DMMA still pays its
+        // fixed issue delay, so rows <= 24 must not run the 4-block code
+        switch ((rows + 7) >> 3) {
+        case 1: mmaTile<NB, 1, MB>(cr, ci, A, Xs, XS, rows, kc, g, t4); break;
+        case 2: mmaTile<NB, 2, MB>(cr, ci, A, Xs, XS, rows, kc, g, t4); break;
+        case 3: mmaTile<NB, 3, MB>(cr, ci, A, Xs, XS, rows, kc, g, t4); break;
+        default: mmaTile<NB, 4, MB>(cr, ci, A, Xs, XS, rows, kc, g, t4); break;
         }
       }
     }

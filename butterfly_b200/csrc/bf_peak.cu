@@ -77,3 +77,41 @@ extern "C" BfCudaStatus bfCudaMeasureFp64Peak(int32_t device, double *dfmaTflops
   if (dmmaTflops) *dmmaTflops = best[1];
   return st;
 }
+
+// Sustained variant: the DMMA loop launched back to back for `seconds`; the figure is the average over
+// the second half, i.e. after the power management has settled (a 1 kW part drops its SM clock under
+// a dense fp64 tensor load).  This is the denominator for a kernel timed inside a long step.
+extern "C" BfCudaStatus bfCudaMeasureFp64PeakSustained(int32_t device, double seconds, double *dmmaTflops) {
+  int prev = -1, nDev = 0;
+  if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0) { cudaGetLastError(); return BF_CUDA_ERROR_NO_DEVICE; }
+  cudaGetDevice(&prev);
+  if (device < 0) device = prev;
+  if (device >= nDev || cudaSetDevice(device) != cudaSuccess) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  if (!(seconds > 0.0) || seconds > 30.0) seconds = 2.0;
+  cudaDeviceProp p;
+  cudaGetDeviceProperties(&p, device);
+  const int sms = p.multiProcessorCount, threads = 256, ctas = sms * 2, iters = 20000;
+  double *out = nullptr;
+  if (cudaMalloc(&out, sizeof(double) * ctas * threads) != cudaSuccess) { cudaSetDevice(prev); return BF_CUDA_ERROR_OUT_OF_MEMORY; }
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+  // one launch is ~5 ms at full clock
+  bfPeakDmma<8><<<ctas, threads>>>(out, iters, 1.0000001, 1e-9);
+  cudaDeviceSynchronize();
+  const int launches = (int)(seconds / 0.0055) + 2, half = launches / 2;
+  cudaEventRecord(e0);
+  for (int i = 0; i < launches; ++i) {
+    if (i == half) cudaEventRecord(e1);
+    bfPeakDmma<8><<<ctas, threads>>>(out, iters, 1.0000001, 1e-9);
+  }
+  cudaEventRecord(e2);
+  BfCudaStatus st = cudaEventSynchronize(e2) == cudaSuccess ? BF_CUDA_OK : BF_CUDA_ERROR_RUNTIME;
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e1, e2);
+  const double flops = 512.0 * 8 * iters * (threads / 32.0) * ctas * (double)(launches - half);
+  if (dmmaTflops) *dmmaTflops = st == BF_CUDA_OK ? flops / ms / 1e9 : 0.0;
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  cudaFree(out);
+  if (prev >= 0) cudaSetDevice(prev);
+  return st;
+}

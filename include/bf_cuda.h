@@ -239,6 +239,10 @@ void bfCudaRawOpsFree(BfCudaPlanDesc *desc);
  * DMMA (mma.sync.m8n8k4.f64) loop, ~20 ms each.  The roofline denominators of the many-RHS apply
  * (bench.py); not used by the apply itself. */
 BfCudaStatus bfCudaMeasureFp64Peak(int32_t device, double *dfmaTflops, double *dmmaTflops);
+/* The DMMA loop launched back to back for `seconds` (default 2), averaged over the second half: the
+ * SUSTAINED fp64 tensor ceiling under the power cap — the denominator for a kernel timed inside a long
+ * step (a 256-RHS apply runs for hundreds of milliseconds). */
+BfCudaStatus bfCudaMeasureFp64PeakSustained(int32_t device, double seconds, double *dmmaTflops);
 const char *bfCudaStatusString(BfCudaStatus status);
 const char *bfCudaLastErrorMessage(void); /* thread-local, human-readable detail */
 int32_t bfCudaAbiVersion(void);

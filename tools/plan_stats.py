@@ -28,3 +28,12 @@ print("rows hist:", np.bincount(rows, minlength=33)[1:])
 print("kc quantiles:", np.percentile(kc, [0, 10, 25, 50, 75, 90, 100]))
 print("mean tile bytes:", (rows * kc * 16).mean())
 sib = T.stage_item_begin if hasattr(T, "stage_item_begin") else None
+# per-stage DMMA fragment efficiency
+for s in range(T.num_stages):
+    tl = T.tiles[T.stage_tile[s]:T.stage_tile[s + 1]]
+    k = tl["kc"].astype(np.int64); r = tl["rows"].astype(np.int64)
+    d = k < 0xFFFE
+    k, r = k[d], r[d]
+    u = (r * k).sum(); p = (((r + 7) // 8 * 8) * ((k + 3) // 4 * 4)).sum()
+    it = T.items[T.stage_item[s]:T.stage_item[s + 1]]
+    print(f"stage {s}: tiles {len(k)} items {len(it)} useful/padded {u / max(p, 1):.3f} mean rows {r.mean():.1f} mean kc {k.mean():.1f} tiles/item {len(k) / max(len(it), 1):.1f} rows%8==0 {np.mean(r % 8 == 0):.2f}")
