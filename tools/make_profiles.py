@@ -20,7 +20,7 @@ for r in rows:
 allus = sum(t for _, t in tot.values())
 with open(P / f"{tag}_launches_bench.csv", "w") as f:
     f.write(f"# ncu launch list, {tag}: `python bench.py --steps 2 --warmup 1 --no-cpu` (helm2 N=524288; 1-RHS applies, fp64 peak probe, 256-RHS side measurement)\n")
-    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 400 ; cold-cache / serialised: compare SHARES\n")
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 500 ; cold-cache / serialised: compare SHARES (bfPeakDmma / bfPeakDfma are the fp64 ceiling probes, not product kernels)\n")
     f.write("kernel,launches,total_us,share_of_captured\n")
     for k, (n, t) in sorted(tot.items(), key=lambda kv: -kv[1][1]):
         f.write(f"\"{k}\",{n},{t:.1f},{t / allus:.4f}\n")
@@ -69,7 +69,7 @@ ir, iw = h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
 scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 gem = [float(r[ir]) * scale[u[ir]] + float(r[iw]) * scale[u[iw]] for r in d]
 h2, u2, d2 = summarise(wide_rep, f"{tag}_wide_mma_full_summary.csv",
-                       "ncu --set full --clock-control none -k regex:bfWideMma -s 16 -c 2 : python bench.py --steps 2 --warmup 1 --no-cpu (N=524288, 256 RHS in 2 chunks of 128); launches = stages 0,1 of one chunk")
+                       "ncu --set full --clock-control none -k regex:bfWideMma -s 16 -c 1 : python bench.py --steps 2 --warmup 1 --no-cpu (N=524288, 256 RHS in 2 chunks of 128); launch = stage 0 of one chunk")
 ir2, iw2 = h2.index("dram__bytes_read.sum"), h2.index("dram__bytes_write.sum")
 wid = [float(r[ir2]) * scale[u2[ir2]] + float(r[iw2]) * scale[u2[iw2]] for r in d2]
 json.dump({"source": f"profiles/{tag}_gemv_full_summary.csv / {tag}_wide_mma_full_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)",
