@@ -183,6 +183,7 @@ ATTACH_EXPORTED_SYMBOLS = [
     "bfCudaMatDetach",
     "bfCudaMatGetPlan",
     "bfCudaMatSetPerms",
+    "bfCudaSolveGMRESMat",
 ]
 
 _lib = None

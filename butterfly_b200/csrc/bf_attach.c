@@ -247,3 +247,46 @@ BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *out
   free(out);
   return st;
 }
+
+/* bfSolveGMRES (src/linalg.c:47) with the Krylov basis resident on the GPU.  Same signature, same
+ * ownership (a non-NULL X0 is consumed: the reference deletes it before returning,
+ * src/linalg.c:312-313), same *numIter.  A must be attached, B (and X0) n x 1 BfMatDenseComplex with
+ * unit column stride, M NULL (the reference's left preconditioner is a host LU solve); anything else
+ * raises BF_ERROR_NOT_IMPLEMENTED like an unimplemented vtable slot would. */
+BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol, BfSize maxNumIter,
+                           BfSize *numIter, BfMat const *M) {
+  if (!isAttached(A) || M != NULL || bfMatGetType(B) != BF_TYPE_MAT_DENSE_COMPLEX ||
+      (X0 != NULL && bfMatGetType(X0) != BF_TYPE_MAT_DENSE_COMPLEX) || bfMatGetNumCols(B) != 1) {
+    bfSetError(BF_ERROR_NOT_IMPLEMENTED);
+    return NULL;
+  }
+  if (maxNumIter == 0 || bfMatGetNumRows(A) != bfMatGetNumCols(A) || bfMatGetNumRows(B) != bfMatGetNumRows(A) ||
+      (X0 != NULL && (bfMatGetNumRows(X0) != bfMatGetNumRows(A) || bfMatGetNumCols(X0) != 1))) {
+    bfSetError(BF_ERROR_INVALID_ARGUMENTS); /* src/linalg.c:80-110 */
+    return NULL;
+  }
+  BfSize n = bfMatGetNumRows(A);
+  BfMatDenseComplex const *Bd = bfMatConstToMatDenseComplexConst(B);
+  BfMatDenseComplex const *X0d = X0 ? bfMatConstToMatDenseComplexConst(X0) : NULL;
+  BfComplex *b = malloc(sizeof(BfComplex) * (n ? n : 1)), *x0 = NULL;
+  for (BfSize i = 0; i < n; ++i) b[i] = Bd->data[i * Bd->rowStride];
+  if (X0d) {
+    x0 = malloc(sizeof(BfComplex) * (n ? n : 1));
+    for (BfSize i = 0; i < n; ++i) x0[i] = X0d->data[i * X0d->rowStride];
+  }
+  BfMatDenseComplex *X = bfMatDenseComplexNew();
+  bfMatDenseComplexInit(X, n, 1);
+  int64_t it = 0;
+  BfCudaStatus st = bfCudaSolveGMRES(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL, NULL);
+  free(b);
+  free(x0);
+  if (X0 != NULL) bfMatDelete(&X0);
+  BfMat *result = bfMatDenseComplexToMat(X);
+  if (st != BF_CUDA_OK) {
+    bfMatDelete(&result);
+    bfSetError(toBfError(st));
+    return NULL;
+  }
+  if (numIter) *numIter = (BfSize)it;
+  return result;
+}

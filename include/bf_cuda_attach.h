@@ -50,6 +50,12 @@ BfCudaPlan *bfCudaMatGetPlan(BfMat const *A);
  * examples/simple/helm2_bie.c:70-81,139) into an attached object's plan. */
 BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *outPerm);
 
+/* Drop-in for bfSolveGMRES (src/linalg.c:47-49, same signature and ownership) on an attached
+ * operator: the Arnoldi process runs on the GPU (bfCudaSolveGMRES) instead of round-tripping every
+ * Krylov vector through bfMatMul.  One complex right-hand side, M == NULL. */
+BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol, BfSize maxNumIter,
+                           BfSize *numIter, BfMat const *M);
+
 #ifdef __cplusplus
 }
 #endif

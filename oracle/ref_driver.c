@@ -299,3 +299,23 @@ double refSolveGMRES(BfMat const *A, const double *b, int64_t n, double tol, int
   *numIter = (int64_t)it;
   return t1 - t0;
 }
+
+/* Helpers for calling a bfSolveGMRES-shaped function pointer (the reference's own, or the attach
+ * layer's bfCudaSolveGMRESMat) from ctypes on an n x 1 complex right-hand side. */
+typedef BfMat *(*RefGmresFn)(BfMat const *, BfMat const *, BfMat *, BfReal, BfSize, BfSize *, BfMat const *);
+double refCallGMRES(RefGmresFn fn, BfMat const *A, const double *b, int64_t n, double tol, int64_t maxNumIter, double *x, int64_t *numIter) {
+  BfMatDenseComplex *B = bfMatDenseComplexNewViewFromPtr((BfSize)n, 1, (BfComplex *)b);
+  BfSize it = 0;
+  double t0 = refNow();
+  BfMat *X = fn(A, bfMatDenseComplexToMat(B), NULL, tol, (BfSize)maxNumIter, &it, NULL);
+  double t1 = refNow();
+  *numIter = X ? (int64_t)it : -1;
+  if (X) {
+    BfMatDenseComplex *Xd = bfMatToMatDenseComplex(X);
+    for (int64_t i = 0; i < n; ++i) memcpy(x + 2 * i, Xd->data + i * Xd->rowStride, sizeof(BfComplex));
+    bfMatDelete(&X);
+  }
+  BfMat *Bm = bfMatDenseComplexToMat(B);
+  bfMatDelete(&Bm);
+  return t1 - t0;
+}

@@ -55,6 +55,7 @@ def load():
         d.refPrintBlocks.argtypes = [vp, C.c_char_p]; d.refPrintBlocks.restype = None
         d.refHelm2MakeSecondKind.argtypes = [vp, dbl]; d.refHelm2MakeSecondKind.restype = None
         d.refSolveGMRES.argtypes = [vp, vp, i64, dbl, i64, vp, vp]; d.refSolveGMRES.restype = dbl
+        d.refCallGMRES.argtypes = [vp, vp, vp, i64, dbl, i64, vp, vp]; d.refCallGMRES.restype = dbl
         _drv = d
     return _drv
 
@@ -134,6 +135,17 @@ class Helm2:
         x = np.zeros_like(b)
         it = C.c_int64()
         t = self.drv.refSolveGMRES(self.mat, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
+        return x, it.value, t
+
+    def solve_gmres_cuda(self, b: np.ndarray, tol: float = 1e-12, max_iter: int = 50):
+        """bfCudaSolveGMRESMat (include/bf_cuda_attach.h): the bfSolveGMRES-shaped entry point of the
+        attach layer, called with reference objects.  The operator must be attached."""
+        a = load_attach()
+        b = np.ascontiguousarray(b, dtype=np.complex128).reshape(-1)
+        x = np.zeros_like(b)
+        it = C.c_int64()
+        fn = C.cast(a.bfCudaSolveGMRESMat, C.c_void_p)
+        t = self.drv.refCallGMRES(fn, self.mat, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
         return x, it.value, t
 
     def flatten(self) -> RawOps:

@@ -32,9 +32,12 @@ def test_device_gmres_matches_bfSolveGMRES(n, k, tol, max_iter):
         # and the reference's own GMRES driving the GPU apply through the swapped vtable
         h.attach()
         x_att, it_att, _ = h.solve_gmres(b, tol, max_iter)
+        # ... and the attach layer's bfSolveGMRES-shaped entry point (Arnoldi on the device)
+        x_dev, it_dev, _ = h.solve_gmres_cuda(b, tol, max_iter)
         h.detach()
-        assert it_att == it_ref
+        assert it_att == it_ref and it_dev == it_ref
         assert np.linalg.norm(x_att - x_ref) / np.linalg.norm(x_ref) <= X_TOL
+        assert np.linalg.norm(x_dev - x_ref) / np.linalg.norm(x_ref) <= X_TOL
     finally:
         h.close()
 
