@@ -189,19 +189,28 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   const unsigned char *pPool = a.pool + a.qPool16[q] * 16ull;
   const unsigned char *cPool = pPool;
 
+  // operand rows of the 1-RHS kernel are dense (ld == 1: bf_capi.cu stages X otherwise, the workspace
+  // has one column), so a row address is base + row * ES with the base picked from two registers
+  const unsigned char *const baseX = a.base[kSpaceX], *const baseW = a.base[kSpaceW];
+  auto inRowPtr = [&](uint32_t addr) -> const unsigned char * {
+    return ((addr >> 30) == kSpaceX ? baseX : baseW) + (size_t)(addr & kRowMask) * ES;
+  };
   auto produce = [&]() {
     while (pT < tEnd) {
       const DevTile t = getTile(pT);
       ++pT;
-      const uint32_t bytes = tileBytes(ES, t.rows, t.kc);
+      if (t.kc >= kKcDiag) { // identity / diagonal tiles are read directly by the consumer
+        pPool += tileBytes(ES, t.rows, t.kc);
+        continue;
+      }
+      const uint32_t bytes = CPLX ? (uint32_t)t.rows * t.kc * 16u : ((uint32_t)t.rows * t.kc * 8u + 15u) & ~15u;
       const unsigned char *src = pPool;
       pPool += bytes;
-      if (t.kc >= kKcDiag) continue; // identity / diagonal tiles are read directly by the consumer
       if (lane == 0) {
         const uint32_t slot = pSeq % kGemvSlots;
         const uint32_t dst = smemU32(ring + slot * kGemvSlotBytes);
         const uint32_t bar = smemU32(&bars[slot]);
-        const unsigned char *xsrc = rowPtr(a, t.inAddr, ES);
+        const unsigned char *xsrc = inRowPtr(t.inAddr);
         uint32_t xb;
         if (CPLX) {
           xb = (uint32_t)t.kc * 16u;
@@ -235,22 +244,21 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
       if (t - twBase >= 32 && pT - twBase >= 32) { tw0 = tw1; twBase += 32; tw1 = loadTiles(twBase + 32); } // both cursors left window 0
       const DevTile tl = getTile(t);
-      const uint32_t bytes = tileBytes(ES, tl.rows, tl.kc);
       if (tl.kc >= kKcDiag) {
         if (lane < rows) {
-          const uint32_t sp = tl.inAddr >> 30;
-          const T xv = *reinterpret_cast<const T *>(rowPtr(a, tl.inAddr, ES) + (long long)lane * a.ld[sp] * ES);
+          const T xv = *reinterpret_cast<const T *>(inRowPtr(tl.inAddr) + (size_t)lane * ES);
           const double d = tl.kc == kKcDiag ? reinterpret_cast<const double *>(cPool)[lane] : 1.0;
           S::fmaReal(extra, d, xv);
         }
-        cPool += bytes;
+        cPool += tileBytes(ES, tl.rows, tl.kc);
         continue;
       }
       const int kc = tl.kc;
+      const uint32_t bytes = CPLX ? (uint32_t)rows * kc * 16u : ((uint32_t)rows * kc * 8u + 15u) & ~15u;
       const uint32_t slot = cSeq % kGemvSlots;
       const unsigned char *As = ring + slot * kGemvSlotBytes;
       const unsigned char *xsB = As + kTileBytes;
-      if (!CPLX) xsB += reinterpret_cast<uintptr_t>(rowPtr(a, tl.inAddr, ES)) & 8u;
+      if (!CPLX) xsB += reinterpret_cast<uintptr_t>(inRowPtr(tl.inAddr)) & 8u;
       mbarWait(smemU32(&bars[slot]), (cSeq / kGemvSlots) & 1u);
 
       const T *xs = reinterpret_cast<const T *>(xsB);
