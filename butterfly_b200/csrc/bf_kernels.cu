@@ -1,16 +1,19 @@
 // bf_kernels.cu — hand-written sm_100a kernels for the butterfly apply.
 //
-// Two stage kernels consume the same stage-major tables and the same packed value pool
+// Three stage kernels consume the same stage-major tables and the same packed value pool
 // (bf_plan.hpp):
-//   bfGemvStage  nrhs == 1.  HBM-bandwidth bound (0.5 flop/B complex, 0.25 real).  One warp owns
-//                one static work queue and streams its contiguous span of the pool through a
-//                private ring of shared-memory slots filled by TMA bulk copies (cp.async.bulk +
-//                mbarrier complete_tx).  The operand segment of every tile rides on the same
-//                mbarrier.  8 (complex) / 16 (real) lanes cooperate on a row: conflict-free 128-byte
-//                LDS phases, operand held in registers, one shuffle reduction per ITEM (not per
-//                tile), one coalesced store.  No atomics: summation order is the plan's order.
-//   bfWideStage  nrhs >= 2.  One CTA owns kWarpsPerCta consecutive queues; RHS columns across
-//                threads, A tiles TMA-staged and read as LDS broadcasts, fp64 FMA pipe bound.
+//   bfGemvStage     nrhs == 1.  HBM-bandwidth bound (0.5 flop/B complex, 0.25 real).  One warp owns
+//                   one static work queue (12 warps / SM) and streams its contiguous span of the pool
+//                   through a private 2-slot ring of shared memory filled by TMA bulk copies
+//                   (cp.async.bulk + mbarrier complete_tx); the operand segment of every tile rides on
+//                   the same mbarrier.  8 (complex) / 16 (real) lanes cooperate on a row: conflict-free
+//                   128-byte LDS phases, operand held in registers, one shuffle reduction per ITEM (not
+//                   per tile), one coalesced store.  Descriptors live in registers across the lanes.
+//                   No atomics: summation order is the plan's order.
+//   bfWideMmaStage  complex, nrhs >= 2.  fp64 tensor pipe (DMMA m8n8k4) bound.  Warp-specialised: a
+//                   producer warp TMA-stages tiles AND operand rows into one byte ring, four consumer
+//                   warps accumulate real / imaginary fragments.
+//   bfWideStage     real, nrhs >= 2.  Register-blocked DFMA (the reference has no such apply).
 //
 // Replaces the per-leaf cblas_zgemm / cblas_dgemv calls of the reference
 // (src/mat_dense_complex.c:1754, src/mat_dense_real.c:1358,1428) and the block loops around
