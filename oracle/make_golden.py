@@ -16,6 +16,11 @@
                          oracle/ref_driver.c refStream*), tol 1e-3; the flattened bfFacSpanGetMat
                          object WITH its factor values, a seeded operand pair and the reference's
                          bfMatMulVec / bfMatRmulVec results.
+  lbo_sphere_fixture.npz the same streamer fed with the reference's own LBO test fixture
+                         (tests/sphere.obj + tests/sphere_{Lam,Phi}.txt, the eigenpairs
+                         tests/test_linalg.c:21-22 checks against): flattened operator, seeded
+                         operands, the reference's bfMatMulVec / bfMatRmulVec results and the
+                         products with the dense eigenvector matrix the factorization approximates.
 """
 import sys
 from pathlib import Path
@@ -120,6 +125,20 @@ def main():
     np.savez_compressed(OUT / "lbo_stream_n600_io.npz", x=xs_, y=ys_, v=vs_, z=zs_, row_perm=st.row_perm(),
                         bands=np.array(st.bands), fingerprint=raw_s.fingerprint())
     print("stream: ops", raw_s.num_ops, "E", raw_s.num_entries, "shape", (st.num_rows, st.num_cols), "bands", st.bands)
+
+    # ---- real path on the reference's own fixture ----
+    sf = reflib.sphere_fixture_stream()
+    raw_f = sf.flatten()
+    xf = rng.standard_normal(sf.num_cols)
+    vf = rng.standard_normal(sf.num_rows)
+    yf, _ = sf.mulvec(xf)
+    zf, _ = sf.mulvec(vf, transposed=True)
+    pf = sf.row_perm()
+    raw_f.save(OUT / "lbo_sphere_fixture.npz")
+    np.savez_compressed(OUT / "lbo_sphere_fixture_io.npz", x=xf, y=yf, v=vf, z=zf, row_perm=pf, bands=np.array(sf.bands),
+                        y_dense=sf.phi[pf] @ xf, z_dense=sf.phi[pf].T @ vf, fingerprint=raw_f.fingerprint())
+    print("fixture stream: ops", raw_f.num_ops, "E", raw_f.num_entries, "shape", (sf.num_rows, sf.num_cols), "bands", sf.bands,
+          "err vs dense Phi", np.linalg.norm(yf - sf.phi[pf] @ xf) / np.linalg.norm(yf))
 
 
 if __name__ == "__main__":

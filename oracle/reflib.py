@@ -17,6 +17,7 @@ from butterfly_b200.rawops import RawOps
 HERE = Path(__file__).resolve().parent
 REF_SO = HERE / "_ref" / "libbutterfly_ref.so"
 DRV_SO = HERE / "_ref" / "libbf_oracle_drv.so"
+REFERENCE = Path("/root/reference")  # only read where it exists (this container), never on the GPU box
 
 _ref = _drv = _att = None
 
@@ -305,4 +306,24 @@ def sphere_stream(n: int = 4000, lmax: int = 31, tol: float = 1e-3, freq_tree_de
 
     s = Stream(pts, fmax, band_fn, freq_tree_depth=freq_tree_depth, tol=tol)
     s.points = pts
+    return s
+
+
+def sphere_fixture_stream(tol: float = 1e-3, freq_tree_depth: int = 2, min_rows: int = 20) -> "Stream":
+    """bfFacStreamer fed with the reference's OWN LBO test fixture: the 500 vertices of tests/sphere.obj
+    and the 32 eigenpairs tests/sphere_{Lam,Phi}.txt that tests/test_linalg.c:21-22 checks its ARPACK
+    solve against.  Frequencies are sqrt(Lam) (src/lbo.c:117-125); the frequency-tree leaves below the
+    lowest fixture frequency receive empty bands."""
+    ref = Path(REFERENCE) / "tests"
+    lam = np.loadtxt(ref / "sphere_Lam.txt")
+    phi = np.loadtxt(ref / "sphere_Phi.txt")
+    pts = np.array([[float(t) for t in ln.split()[1:4]] for ln in open(ref / "sphere.obj") if ln.startswith("v ")])
+    freqs = np.sqrt(lam)
+
+    def band_fn(a, b, leftmost, rightmost):
+        sel = [i for i in range(len(freqs)) if (leftmost or freqs[i] >= a) and (rightmost or freqs[i] < b)]
+        return phi[:, sel], freqs[sel]
+
+    s = Stream(pts, float(freqs.max()) * 1.0001, band_fn, freq_tree_depth=freq_tree_depth, tol=tol, min_rows=min_rows, min_cols=1)
+    s.points, s.phi, s.freqs = pts, phi, freqs
     return s

@@ -79,11 +79,13 @@ def test_fused_tree_permutation_matches_bfMatPermuteRows():
 
 
 # ---- real path (configs[3]: LBO-style streamed butterfly, forward and transpose) ------------------
-def test_golden_stream_on_gpu():
-    """The streamed real operator with the reference's factor values, against the reference's own
-    bfMatMulVec / bfMatRmulVec outputs (tests/golden, no reference needed at run time)."""
-    raw = RawOps.load(G / "lbo_stream_n600.npz")
-    io = np.load(G / "lbo_stream_n600_io.npz")
+@pytest.mark.parametrize("name", ["lbo_stream_n600", "lbo_sphere_fixture"])
+def test_golden_stream_on_gpu(name):
+    """The streamed real operators with the reference's factor values (spherical harmonics on 600 points;
+    the reference's own tests/sphere_{Lam,Phi}.txt fixture), against the reference's own bfMatMulVec /
+    bfMatRmulVec outputs (tests/golden, no reference needed at run time)."""
+    raw = RawOps.load(G / f"{name}.npz")
+    io = np.load(G / f"{name}_io.npz")
     with Plan(raw, build_transpose=1) as plan:
         y = plan.apply_host(io["x"], capi.OP_N)
         z = plan.apply_host(io["v"], capi.OP_T)

@@ -99,6 +99,32 @@ def test_compiled_tables_reproduce_reference_real_path(stream, op, xin, yout):
     assert np.linalg.norm(y - io[yout]) / np.linalg.norm(io[yout]) < 1e-13
 
 
+@pytest.fixture(scope="module")
+def fixture_stream():
+    return RawOps.load(G / "lbo_sphere_fixture.npz"), np.load(G / "lbo_sphere_fixture_io.npz")
+
+
+@pytest.mark.parametrize("op,xin,yout", [(capi.OP_N, "x", "y"), (capi.OP_T, "v", "z")])
+def test_reference_sphere_fixture_factorization(fixture_stream, op, xin, yout):
+    """bfFacStreamer run on the reference's own LBO test data (tests/sphere.obj, sphere_{Lam,Phi}.txt,
+    the eigenpairs of tests/test_linalg.c:21-22): port oracle and compiled tables against the reference's
+    bfMatMulVec / bfMatRmulVec, and both within the streamer's tolerance of the dense eigenvector matrix."""
+    raw, io = fixture_stream
+    assert raw.dtype == capi.REAL_F64 and (raw.num_rows, raw.num_cols) == (500, 32)
+    assert np.array_equal(raw.fingerprint(), io["fingerprint"])
+    y = portlib.apply(raw, io[xin][:, None], op)[:, 0]
+    assert np.linalg.norm(y - io[yout]) / np.linalg.norm(io[yout]) < 1e-13
+    t = Tables(raw, op, 148 * 12)
+    try:
+        t.check_queues()
+        yt = t.apply(io[xin])[:, 0]
+    finally:
+        t.close()
+    assert np.linalg.norm(yt - io[yout]) / np.linalg.norm(io[yout]) < 1e-13
+    dense = io[yout + "_dense"]
+    assert np.linalg.norm(yt - dense) / np.linalg.norm(dense) < 1e-3   # tol handed to bfFacStreamerInit
+
+
 def test_streamed_operator_contains_identity_leaves(stream):
     raw, _ = stream
     kinds = set(raw.ops["kind"].tolist())

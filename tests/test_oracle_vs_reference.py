@@ -107,3 +107,14 @@ def test_stream_vs_dense_band_pin(stream):
     x = np.random.default_rng(1).standard_normal(stream.num_cols)
     y, _ = stream.mulvec(x)
     assert np.abs(y - Bp @ x).max() / np.abs(Bp @ x).max() < 5e-3
+
+
+def test_sphere_fixture_golden_is_reproducible():
+    """The committed lbo_sphere_fixture golden is what the reference produces today from its own test data."""
+    s = reflib.sphere_fixture_stream()
+    raw = s.flatten()
+    io = np.load(G / "lbo_sphere_fixture_io.npz")
+    assert np.array_equal(raw.fingerprint(), io["fingerprint"])
+    y, _ = s.mulvec(io["x"])
+    assert np.linalg.norm(y - io["y"]) / np.linalg.norm(io["y"]) < 1e-14
+    assert np.array_equal(s.row_perm(), io["row_perm"])
