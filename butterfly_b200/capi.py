@@ -178,6 +178,7 @@ EXPORTED_SYMBOLS = [
 DEBUG_EXPORTED_SYMBOLS = ["bfCudaDebugCompile", "bfCudaDebugFree"]
 ATTACH_EXPORTED_SYMBOLS = [
     "bfCudaFlatten",
+    "bfCudaFlattenEx",
     "bfCudaFlattenFree",
     "bfCudaMatAttach",
     "bfCudaMatDetach",

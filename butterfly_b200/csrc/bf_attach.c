@@ -186,7 +186,7 @@ BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) {
   if (!A) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   if (isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   BfCudaPlanDesc *desc = NULL;
-  BfCudaStatus st = bfCudaFlatten(A, &desc);
+  BfCudaStatus st = bfCudaFlattenEx(A, opts ? opts->flattenFlags : 0u, &desc);
   if (st != BF_CUDA_OK) return st;
   desc->device = opts ? opts->device : -1;
   desc->buildTranspose = opts ? opts->buildTranspose : 0;
@@ -209,8 +209,10 @@ BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) {
   w->vt.MulVec = attachedMulVec;
   w->vt.Rmul = attachedRmul;
   w->vt.RmulVec = attachedRmulVec;
-  w->vt.NumBytes = attachedNumBytes;
-  w->vt.Delete = attachedDelete;
+  /* slots the type leaves empty stay empty (MatSum has neither, src/mat_sum.c:12-17: such an object
+   * is freed with its own Deinit after bfCudaMatDetach) */
+  if (w->orig->NumBytes) w->vt.NumBytes = attachedNumBytes;
+  if (w->orig->Delete) w->vt.Delete = attachedDelete;
   A->vtbl = &w->vt;
   return BF_CUDA_OK;
 }

@@ -9,6 +9,10 @@
  *   MatBlockCoo    k = 0..numBlocks-1 in storage order                   src/mat_block_coo.c:404-418
  *   MatBlockDense  i outer, j inner, block[i*numColBlocks + j]           src/mat_block_dense.c:534-566
  *   MatSum         terms in order                                        src/mat_sum.c:54
+ *   MatCooComplex  the Kapur-Rokhlin correction term bfMatBlockDenseAddInplace wraps into a MatSum
+ *                  next to a butterfly (src/mat_block_dense.c:458-510, src/quadrature.c:126-167):
+ *                  turned into a few small dense leaves over the clusters of its nonzeros
+ *                  (buffers owned by the descriptor)                     src/mat_coo_complex.c:212-262
  */
 #include "bf_cuda_attach.h"
 
@@ -19,6 +23,7 @@
 #include <bf/mat_block_coo.h>
 #include <bf/mat_block_dense.h>
 #include <bf/mat_block_diag.h>
+#include <bf/mat_coo_complex.h>
 #include <bf/mat_dense_complex.h>
 #include <bf/mat_dense_real.h>
 #include <bf/mat_diag_real.h>
@@ -32,8 +37,33 @@ typedef struct Flat {
   int64_t *bufRows;
   int64_t numBufs, capBufs;
   int dtype; /* -1 until the first dense leaf is seen */
+  uint32_t flags; /* BF_CUDA_FLATTEN_* */
+  void **owned; /* dense buffers made for sparse leaves */
+  int64_t numOwned, capOwned;
   BfCudaStatus status;
 } Flat;
+
+/* What bfCudaFlatten hands out: the public descriptor followed by the buffers it owns. */
+typedef struct FlatDesc {
+  BfCudaPlanDesc desc;
+  void **owned;
+  int64_t numOwned;
+} FlatDesc;
+
+static void *newOwned(Flat *f, size_t bytes) {
+  if (f->status != BF_CUDA_OK) return NULL;
+  if (f->numOwned == f->capOwned) {
+    int64_t cap = f->capOwned ? 2 * f->capOwned : 64;
+    void **p = realloc(f->owned, (size_t)cap * sizeof *p);
+    if (!p) { f->status = BF_CUDA_ERROR_OUT_OF_MEMORY; return NULL; }
+    f->owned = p;
+    f->capOwned = cap;
+  }
+  void *buf = calloc(1, bytes ? bytes : 1);
+  if (!buf) { f->status = BF_CUDA_ERROR_OUT_OF_MEMORY; return NULL; }
+  f->owned[f->numOwned++] = buf;
+  return buf;
+}
 
 static void pushOp(Flat *f, BfCudaRawOp const *op) {
   if (f->status != BF_CUDA_OK) return;
@@ -78,6 +108,88 @@ static void emitBlocks(Flat *f, BfMatBlock const *mb, BfSize numBlocks, BfSize c
     emit(f, block, inBuf, inOff + (int64_t)mb->colOffset[j], outBuf,
          outOff + (int64_t)mb->rowOffset[i]);
   }
+}
+
+/* ---- sparse correction terms ------------------------------------------------------------------ */
+typedef struct CooEnt {
+  int64_t i, j;
+  BfComplex z;
+} CooEnt;
+
+static int cmpRow(const void *a, const void *b) {
+  CooEnt const *x = a, *y = b;
+  return x->i != y->i ? (x->i < y->i ? -1 : 1) : (x->j != y->j ? (x->j < y->j ? -1 : 1) : 0);
+}
+
+static int cmpCol(const void *a, const void *b) {
+  CooEnt const *x = a, *y = b;
+  return x->j != y->j ? (x->j < y->j ? -1 : 1) : (x->i != y->i ? (x->i < y->i ? -1 : 1) : 0);
+}
+
+/* One dense leaf over the bounding box of e[0..n) if the box is not much larger than its nonzeros,
+ * else split at the widest gap of the longer side and recurse. */
+static void emitCooCluster(Flat *f, CooEnt *e, int64_t n, BfCudaRawOp const *proto) {
+  if (f->status != BF_CUDA_OK || n == 0) return;
+  int64_t i0 = e[0].i, i1 = e[0].i, j0 = e[0].j, j1 = e[0].j;
+  for (int64_t t = 1; t < n; ++t) {
+    if (e[t].i < i0) i0 = e[t].i;
+    if (e[t].i > i1) i1 = e[t].i;
+    if (e[t].j < j0) j0 = e[t].j;
+    if (e[t].j > j1) j1 = e[t].j;
+  }
+  int64_t h = i1 - i0 + 1, w = j1 - j0 + 1;
+  if (h * w <= 8 * n + 64) {
+    BfComplex *buf = newOwned(f, (size_t)(h * w) * sizeof(BfComplex));
+    if (!buf) return;
+    for (int64_t t = 0; t < n; ++t) buf[(e[t].i - i0) * w + (e[t].j - j0)] += e[t].z;
+    BfCudaRawOp op = *proto;
+    op.kind = BF_CUDA_LEAF_DENSE;
+    op.inOff += j0; op.outOff += i0;
+    op.m = h; op.k = w; op.ld = w;
+    op.val = buf;
+    pushOp(f, &op);
+    return;
+  }
+  int byRow = h >= w;
+  qsort(e, (size_t)n, sizeof *e, byRow ? cmpRow : cmpCol);
+  int64_t cut = n / 2, best = -1;
+  for (int64_t t = 1; t < n; ++t) {
+    int64_t gap = byRow ? e[t].i - e[t - 1].i : e[t].j - e[t - 1].j;
+    if (gap > best) { best = gap; cut = t; }
+  }
+  emitCooCluster(f, e, cut, proto);
+  emitCooCluster(f, e + cut, n - cut, proto);
+}
+
+static void emitCooComplex(Flat *f, BfMat const *mat, BfCudaRawOp const *proto) {
+  BfMatCooComplex const *coo = bfMatConstToMatCooComplexConst(mat);
+  if (mat->props & (BF_MAT_PROPS_TRANS | BF_MAT_PROPS_CONJ)) { f->status = BF_CUDA_ERROR_NOT_IMPLEMENTED; return; }
+  setDtype(f, BF_CUDA_COMPLEX_F64);
+  int64_t n = (int64_t)coo->numElts, m = (int64_t)bfMatGetNumRows(mat);
+  if (n == 0 || f->status != BF_CUDA_OK) return;
+  CooEnt *e = malloc((size_t)n * sizeof *e);
+  int64_t *lastOfRow = NULL;
+  if (!e) { f->status = BF_CUDA_ERROR_OUT_OF_MEMORY; return; }
+  int64_t cnt = 0;
+  if (f->flags & BF_CUDA_FLATTEN_COO_ACCUMULATE) {
+    for (int64_t t = 0; t < n; ++t) e[cnt++] = (CooEnt){(int64_t)coo->rowInd[t], (int64_t)coo->colInd[t], coo->value[t]};
+  } else {
+    /* The reference's product ASSIGNS row i of the result for every stored element
+     * (`*outPtr = *inPtr; *outPtr *= z;`, src/mat_coo_complex.c:248-251): of several elements in one
+     * row only the last in storage order survives.  Reproduced here. */
+    lastOfRow = malloc((size_t)m * sizeof *lastOfRow);
+    if (!lastOfRow) { free(e); f->status = BF_CUDA_ERROR_OUT_OF_MEMORY; return; }
+    for (int64_t r = 0; r < m; ++r) lastOfRow[r] = -1;
+    for (int64_t t = 0; t < n; ++t) lastOfRow[coo->rowInd[t]] = t;
+    for (int64_t r = 0; r < m; ++r)
+      if (lastOfRow[r] >= 0) {
+        int64_t t = lastOfRow[r];
+        e[cnt++] = (CooEnt){r, (int64_t)coo->colInd[t], coo->value[t]};
+      }
+    free(lastOfRow);
+  }
+  emitCooCluster(f, e, cnt, proto);
+  free(e);
 }
 
 static void emit(Flat *f, BfMat const *mat, int64_t inBuf, int64_t inOff, int64_t outBuf,
@@ -134,6 +246,9 @@ static void emit(Flat *f, BfMat const *mat, int64_t inBuf, int64_t inOff, int64_
   }
   case BF_TYPE_MAT_ZERO:
     return;
+  case BF_TYPE_MAT_COO_COMPLEX:
+    emitCooComplex(f, mat, &op);
+    return;
   case BF_TYPE_MAT_PRODUCT: {
     BfMatProduct const *prod = bfMatConstToMatProductConst(mat);
     BfSize L = bfMatProductNumFactors(prod);
@@ -182,18 +297,26 @@ static void emit(Flat *f, BfMat const *mat, int64_t inBuf, int64_t inOff, int64_
   }
   default:
     /* MatPerm (no Mul in the reference, src/mat_perm.c:53-61), MatFunc, MatPython, MatCsrReal,
-     * MatCoo*, MatDiff, MatGivens: refused. */
+     * MatCooReal (no Mul either), MatDiff, MatGivens: refused. */
     f->status = BF_CUDA_ERROR_NOT_IMPLEMENTED;
     return;
   }
 }
 
-BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **out) {
+static void freeOwned(void **owned, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) free(owned[i]);
+  free(owned);
+}
+
+BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **out) { return bfCudaFlattenEx(A, 0, out); }
+
+BfCudaStatus bfCudaFlattenEx(BfMat const *A, uint32_t flags, BfCudaPlanDesc **out) {
   if (!A || !out) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   *out = NULL;
   Flat f;
   memset(&f, 0, sizeof f);
   f.dtype = -1;
+  f.flags = flags;
   f.status = BF_CUDA_OK;
   int64_t numRows = (int64_t)bfMatGetNumRows(A), numCols = (int64_t)bfMatGetNumCols(A);
   newBuf(&f, numCols); /* BF_CUDA_BUF_X */
@@ -202,10 +325,14 @@ BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **out) {
   if (f.status != BF_CUDA_OK) {
     free(f.ops);
     free(f.bufRows);
+    freeOwned(f.owned, f.numOwned);
     return f.status;
   }
-  BfCudaPlanDesc *d = calloc(1, sizeof *d);
-  if (!d) { free(f.ops); free(f.bufRows); return BF_CUDA_ERROR_OUT_OF_MEMORY; }
+  FlatDesc *fd = calloc(1, sizeof *fd);
+  if (!fd) { free(f.ops); free(f.bufRows); freeOwned(f.owned, f.numOwned); return BF_CUDA_ERROR_OUT_OF_MEMORY; }
+  fd->owned = f.owned;
+  fd->numOwned = f.numOwned;
+  BfCudaPlanDesc *d = &fd->desc;
   d->abiVersion = BF_CUDA_ABI_VERSION;
   d->dtype = f.dtype < 0 ? BF_CUDA_REAL_F64 : f.dtype;
   d->numRows = numRows;
@@ -222,7 +349,9 @@ BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **out) {
 
 void bfCudaFlattenFree(BfCudaPlanDesc *desc) {
   if (!desc) return;
+  FlatDesc *fd = (FlatDesc *)desc; /* desc is the first member */
   free((void *)desc->ops);
   free((void *)desc->bufRows);
-  free(desc);
+  freeOwned(fd->owned, fd->numOwned);
+  free(fd);
 }

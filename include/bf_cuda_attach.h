@@ -29,14 +29,24 @@ extern "C" {
 typedef struct BfCudaAttachOpts {
   int32_t device;         /* CUDA device ordinal, -1 = current */
   int32_t buildTranspose; /* also compile A^T / A^H (needed by Rmul / RmulVec) */
+  uint32_t flattenFlags;  /* BF_CUDA_FLATTEN_* */
 } BfCudaAttachOpts;
+
+/* MatCooComplex leaves: by default several stored elements in one row behave as in the reference's
+ * bfMatCooComplexMul, where each element OVERWRITES its result row (src/mat_coo_complex.c:248-251), so
+ * only the last one counts.  With this flag they are summed, i.e. the sparse matrix is applied as the
+ * matrix it stores. */
+#define BF_CUDA_FLATTEN_COO_ACCUMULATE 1u
 
 /* Flatten `A` into raw ops (bf_cuda.h).  Values are NOT copied: ops point into the leaves of
  * `A`, which must outlive the returned descriptor's use.  Supported nodes: MatProduct,
  * MatBlockDense, MatBlockDiag, MatBlockCoo, MatSum, MatDenseComplex, MatDenseReal, MatIdentity,
- * MatDiagReal, MatZero.  Anything else (MatPerm has no Mul in the reference either,
- * src/mat_perm.c:53-61) -> BF_CUDA_ERROR_NOT_IMPLEMENTED. */
+ * MatDiagReal, MatZero, and MatCooComplex (Kapur-Rokhlin correction terms inside a MatSum,
+ * src/mat_block_dense.c:458-510), which becomes dense leaves in buffers the descriptor owns.  Anything
+ * else (MatPerm has no Mul in the reference either, src/mat_perm.c:53-61) ->
+ * BF_CUDA_ERROR_NOT_IMPLEMENTED. */
 BfCudaStatus bfCudaFlatten(BfMat const *A, BfCudaPlanDesc **desc);
+BfCudaStatus bfCudaFlattenEx(BfMat const *A, uint32_t flags, BfCudaPlanDesc **desc);
 void bfCudaFlattenFree(BfCudaPlanDesc *desc);
 
 /* Flatten + compile + upload + swap the vtable.  The plan is a snapshot: in-place edits of `A`

@@ -15,14 +15,18 @@
 #include <bf/helm2.h>
 #include <bf/layer_pot.h>
 #include <bf/linalg.h>
+#include <complex.h>
+#include <bf/mat_coo_complex.h>
 #include <bf/mat_dense_complex.h>
 #include <bf/mat_dense_real.h>
+#include <bf/mat_sum.h>
 #include <bf/points.h>
 #include <bf/quadtree.h>
 #include <bf/rand.h>
 #include <bf/util.h>
 #include <bf/vec_complex.h>
 #include <bf/vec_real.h>
+#include <bf/vectors.h>
 
 typedef struct RefHelm2 {
   double *pointData;
@@ -85,6 +89,11 @@ void refHelm2DenseKernel(RefHelm2 *h, double *out) {
 
 void refHelm2Free(RefHelm2 *h) {
   if (!h) return;
+  if (h->A && bfMatGetType(h->A) == BF_TYPE_MAT_SUM) { /* MatSum has no Delete slot (src/mat_sum.c:12-17) */
+    BfMatSum *sum = (BfMatSum *)h->A;
+    bfMatSumDeinitAndDealloc(&sum);
+    h->A = NULL;
+  }
   if (h->A) bfMatDelete(&h->A);
   bfQuadtreeDeinit(&h->quadtree);
   free(h->pointData);
@@ -281,6 +290,37 @@ void refHelm2MakeSecondKind(RefHelm2 *h, double weight) {
   BfMat *oneHalfEye = bfMatDiagRealToMat(bfMatDiagRealNewConstant(n, n, 0.5));
   bfMatAddInplace(h->A, oneHalfEye);
   bfMatDelete(&oneHalfEye);
+}
+
+/* Kapur-Rokhlin correction of the multilevel butterfly as multiple_scattering_context.c:467-472 applies
+ * it (one closed curve: bfHelm2ApplyKrCorrectionTree, src/helm2.c:398-414).  Butterflied blocks that
+ * receive correction entries become MatSum [MatProduct, MatCooComplex] (src/mat_block_dense.c:493-499).
+ * The single-layer kernel ignores the normals; a zero array keeps krComplexKernel's indexing valid. */
+void refHelm2ApplyKrCorrection(RefHelm2 *h, int64_t order) {
+  BfSize n = bfMatGetNumRows(h->A);
+  BfVectors2 normals = {.data = calloc(n, sizeof(BfVector2)), .size = n, .capacity = n, .isView = true};
+  bfHelm2ApplyKrCorrectionTree(&h->helm, (BfSize)order, h->points, &normals, bfQuadtreeToTree(&h->quadtree), h->A);
+  free(normals.data);
+}
+
+/* A <- MatSum [A, C] for an n x n MatCooComplex C (tree order): the node bfMatBlockDenseAddInplace
+ * builds around a butterflied block that receives correction entries (src/mat_block_dense.c:493-499),
+ * here with terms that stay alive — the reference deletes the sparse term it has just put into the
+ * sum (`next: bfMatDelete(&otherBlock)`, :502-503), so sums made by that routine cannot be applied. */
+void refHelm2SumWithCoo(RefHelm2 *h, int64_t nnz, const int64_t *rowInd, const int64_t *colInd, const double *values) {
+  BfSize n = bfMatGetNumRows(h->A);
+  BfMatCooComplex *coo = bfMatCooComplexNew();
+  bfMatCooComplexInitEmpty(coo, n, n, (BfSize)nnz);
+  for (int64_t t = 0; t < nnz; ++t) {
+    coo->rowInd[t] = (BfSize)rowInd[t];
+    coo->colInd[t] = (BfSize)colInd[t];
+    coo->value[t] = values[2 * t] + I * values[2 * t + 1];
+  }
+  BfMatSum *sum = bfMatSumNew();
+  bfMatSumInit(sum);
+  bfMatSumAddTerm(sum, h->A);
+  bfMatSumAddTerm(sum, bfMatCooComplexToMat(coo));
+  h->A = bfMatSumToMat(sum);
 }
 
 /* X = bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, NULL) (src/linalg.c:47), B n x 1 complex.

@@ -69,10 +69,11 @@ def load_attach():
         capi.load_library()
         a = C.CDLL(str(capi.ATTACH_LIB_PATH), mode=C.RTLD_GLOBAL)
         a.bfCudaFlatten.argtypes = [C.c_void_p, C.POINTER(C.POINTER(capi.PlanDesc))]; a.bfCudaFlatten.restype = C.c_int32
+        a.bfCudaFlattenEx.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.POINTER(capi.PlanDesc))]; a.bfCudaFlattenEx.restype = C.c_int32
         a.bfCudaFlattenFree.argtypes = [C.POINTER(capi.PlanDesc)]; a.bfCudaFlattenFree.restype = None
 
         class AttachOpts(C.Structure):
-            _fields_ = [("device", C.c_int32), ("buildTranspose", C.c_int32)]
+            _fields_ = [("device", C.c_int32), ("buildTranspose", C.c_int32), ("flattenFlags", C.c_uint32)]
 
         a.AttachOpts = AttachOpts
         a.bfCudaMatAttach.argtypes = [C.c_void_p, C.POINTER(AttachOpts)]; a.bfCudaMatAttach.restype = C.c_int32
@@ -129,6 +130,24 @@ class Helm2:
         2 pi / n of the unit circle by default."""
         self.drv.refHelm2MakeSecondKind(self.h, float(2 * np.pi / self.n if weight is None else weight))
 
+    def apply_kr_correction(self, order: int = 6):
+        """bfHelm2ApplyKrCorrectionTree (src/helm2.c:398-414): Kapur-Rokhlin correction entries added to
+        the operator in place; butterflied blocks they touch become MatSum [MatProduct, MatCooComplex]."""
+        self.drv.refHelm2ApplyKrCorrection.argtypes = [C.c_void_p, C.c_int64]
+        self.drv.refHelm2ApplyKrCorrection.restype = None
+        self.drv.refHelm2ApplyKrCorrection(self.h, int(order))
+
+    def sum_with_coo(self, rows: np.ndarray, cols: np.ndarray, values: np.ndarray):
+        """A <- MatSum [A, C] for an n x n MatCooComplex C in tree order (the shape of a butterfly with
+        sparse correction entries, src/mat_block_dense.c:493-499)."""
+        r = np.ascontiguousarray(rows, dtype=np.int64)
+        c = np.ascontiguousarray(cols, dtype=np.int64)
+        v = np.ascontiguousarray(values, dtype=np.complex128)
+        self.drv.refHelm2SumWithCoo.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.drv.refHelm2SumWithCoo.restype = None
+        self.drv.refHelm2SumWithCoo(self.h, len(r), r.ctypes.data, c.ctypes.data, v.ctypes.data)
+        self.mat = self.drv.refHelm2GetMat(self.h)
+
     def solve_gmres(self, b: np.ndarray, tol: float = 1e-12, max_iter: int = 50):
         """bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, NULL) (src/linalg.c:47) through the
         object's CURRENT vtable.  Returns (x, num_iter, seconds)."""
@@ -149,10 +168,10 @@ class Helm2:
         t = self.drv.refCallGMRES(fn, self.mat, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
         return x, it.value, t
 
-    def flatten(self) -> RawOps:
+    def flatten(self, flags: int = 0) -> RawOps:
         a = load_attach()
         d = C.POINTER(capi.PlanDesc)()
-        st = a.bfCudaFlatten(self.mat, C.byref(d))
+        st = a.bfCudaFlattenEx(self.mat, flags, C.byref(d))
         if st != 0:
             raise RuntimeError(f"bfCudaFlatten: status {st}")
         try:
@@ -160,9 +179,9 @@ class Helm2:
         finally:
             a.bfCudaFlattenFree(d)
 
-    def attach(self, build_transpose=0):
+    def attach(self, build_transpose=0, flatten_flags=0):
         a = load_attach()
-        o = a.AttachOpts(-1, build_transpose)
+        o = a.AttachOpts(-1, build_transpose, flatten_flags)
         st = a.bfCudaMatAttach(self.mat, C.byref(o))
         if st != 0:
             raise capi.BfCudaError(st, "bfCudaMatAttach", capi.load_library().bfCudaLastErrorMessage().decode())

@@ -60,6 +60,45 @@ def test_bfmatmul_through_swapped_vtable(n, k):
 
 
 @needs_ref
+def test_corrected_system_matrix_through_swapped_vtable():
+    """The multiple-scattering system matrix (multiple_scattering_context.c:456-487): Kapur-Rokhlin
+    correction, column weights, + I/2, and a sparse MatCooComplex term in a MatSum next to the
+    butterflies (src/mat_block_dense.c:493-499) — the reference's bfMatMul before and after attaching."""
+    n = 2048
+    h = reflib.Helm2(reflib.circle_points(n), 50.0)
+    try:
+        h.apply_kr_correction(6)
+        h.make_second_kind()
+        rng = np.random.default_rng(5)
+        rows, cols = rng.integers(0, n, 1500), rng.integers(0, n, 1500)
+        rows = np.concatenate([rows, np.repeat(np.arange(100, 140), 3)])
+        cols = np.concatenate([cols, 1500 + rng.integers(0, 40, 120)])
+        vals = rng.standard_normal(len(rows)) + 1j * rng.standard_normal(len(rows))
+        h.sum_with_coo(rows, cols, vals)
+        x = reflib.randn_complex(n, 0)
+        X = np.stack([x, np.conj(x), 1j * np.roll(x, 3)], axis=1)
+        y_cpu, _ = h.matmul(x)
+        Y_cpu, _ = h.matmul(X)
+        h.attach()
+        y_gpu, _ = h.matmul(x)
+        Y_gpu, _ = h.matmul(X)
+        h.detach()
+        assert np.linalg.norm(y_gpu - y_cpu) / np.linalg.norm(y_cpu) <= TOL
+        for c in range(X.shape[1]):
+            assert np.linalg.norm(Y_gpu[:, c] - Y_cpu[:, c]) / np.linalg.norm(Y_cpu[:, c]) <= TOL
+        # the sparse term applied as the matrix it stores (entries of a row summed)
+        D = np.zeros((n, n), np.complex128)
+        np.add.at(D, (rows, cols), vals)
+        raw_acc = h.flatten(flags=1)
+        with Plan(raw_acc) as plan:
+            y_acc = plan.apply_host(x)
+        want = portlib.apply(raw_acc, x[:, None])[:, 0]
+        assert np.linalg.norm(y_acc - want) / np.linalg.norm(want) <= TOL
+    finally:
+        h.close()
+
+
+@needs_ref
 def test_fused_tree_permutation_matches_bfMatPermuteRows():
     """Callers permute around the apply (examples/simple/helm2_bie.c:70-81,139); fused into the
     plan the result must be bit-identical to permuting with the reference's own routine."""

@@ -64,6 +64,56 @@ def test_butterfly_vs_dense_kernel_pin(helm):
     assert np.linalg.norm(y[:, 0] - yd) / np.linalg.norm(yd) < 1e-11
 
 
+def _correction_entries(n, rng):
+    """Scattered entries (most land in butterflied blocks) plus a cluster with several entries per row."""
+    r = rng.integers(0, n, 1500)
+    c = rng.integers(0, n, 1500)
+    r2 = np.repeat(np.arange(100, 140), 3)
+    c2 = 1500 + rng.integers(0, 40, len(r2))
+    rows, cols = np.concatenate([r, r2]), np.concatenate([c, c2])
+    return rows, cols, rng.standard_normal(len(rows)) + 1j * rng.standard_normal(len(rows))
+
+
+def test_kapur_rokhlin_corrected_operator_and_sparse_sum_term():
+    """The corrected system matrix of examples/multiple_scattering (multiple_scattering_context.c:456-487):
+    bfHelm2ApplyKrCorrectionTree edits the near-field leaves in place; a MatSum [operator, MatCooComplex]
+    carries sparse entries next to butterflied blocks (src/mat_block_dense.c:493-499).  Reference
+    bfMatMul vs flattener + port oracle + compiled tables; then the same sparse term with its entries
+    summed (BF_CUDA_FLATTEN_COO_ACCUMULATE) against dense arithmetic."""
+    n = 2048
+    h = reflib.Helm2(reflib.circle_points(n), 50.0)
+    try:
+        x = reflib.randn_complex(n, 0)
+        y_plain, _ = h.matmul(x)
+        h.apply_kr_correction(6)
+        y_kr, _ = h.matmul(x)
+        assert np.linalg.norm(y_kr - y_plain) > 1e-3 * np.linalg.norm(y_plain)   # the correction did something
+        raw_kr = h.flatten()
+        y0 = portlib.apply(raw_kr, x[:, None])
+        assert np.linalg.norm(y0 - y_kr) / np.linalg.norm(y_kr) < 1e-13
+
+        rows, cols, vals = _correction_entries(n, np.random.default_rng(5))
+        h.sum_with_coo(rows, cols, vals)
+        y_ref, _ = h.matmul(x)                       # bfMatSumMul -> bfMatCooComplexMul (last entry of a row wins)
+        raw = h.flatten()
+        assert raw.num_ops > raw_kr.num_ops
+        assert np.linalg.norm(portlib.apply(raw, x[:, None]) - y_ref) / np.linalg.norm(y_ref) < 1e-13
+        t = Tables(raw, capi.OP_N, 148 * 12)
+        try:
+            t.check_queues()
+            assert np.linalg.norm(t.apply(x) - y_ref) / np.linalg.norm(y_ref) < 1e-13
+        finally:
+            t.close()
+
+        raw_acc = h.flatten(flags=1)                 # BF_CUDA_FLATTEN_COO_ACCUMULATE
+        D = np.zeros((n, n), np.complex128)
+        np.add.at(D, (rows, cols), vals)
+        want = y0 + (D @ x)[:, None]
+        assert np.linalg.norm(portlib.apply(raw_acc, x[:, None]) - want) / np.linalg.norm(want) < 1e-13
+    finally:
+        h.close()
+
+
 # ---- real (streamed) path: live bfFacStreamer factorization --------------------------------------
 @pytest.fixture(scope="module")
 def stream():
