@@ -219,7 +219,8 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
         from butterfly_b200 import gmres
 
         bvec = x[:, 0].clone()
-        for orth in ("mgs", "cgs"):
+        gmres.solve_gmres_sharded(op, bvec, None, 0.0, 2, "cgs")  # warm-up: communicators, allocator
+        for orth in ("mgs", "cgs", "cgs2"):
             barrier()
             t0 = time.perf_counter()
             _, its, resid, napp = gmres.solve_gmres_sharded(op, bvec, None, 0.0, args.solve, orth)

@@ -165,6 +165,10 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanGetWorkspace",
     "bfCudaPlanGetWorkspaceLayout",
     "bfCudaSolveGMRES",
+    "bfCudaGmresScratchBytes",
+    "bfCudaGmresProject",
+    "bfCudaGmresSubtract",
+    "bfCudaGmresScale",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
@@ -264,6 +268,14 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaPlanGetStream.restype = vp
     lib.bfCudaSolveGMRES.argtypes = [vp, vp, vp, C.c_double, i64, vp, C.POINTER(i64), C.POINTER(C.c_double), C.POINTER(i64)]
     lib.bfCudaSolveGMRES.restype = i32
+    lib.bfCudaGmresScratchBytes.argtypes = [i64]
+    lib.bfCudaGmresScratchBytes.restype = i64
+    lib.bfCudaGmresProject.argtypes = [vp, i64, i64, vp, i64, vp, vp, vp]
+    lib.bfCudaGmresProject.restype = i32
+    lib.bfCudaGmresSubtract.argtypes = [vp, i64, i64, vp, vp, i64, vp, vp, vp]
+    lib.bfCudaGmresSubtract.restype = i32
+    lib.bfCudaGmresScale.argtypes = [vp, i64, vp, vp, vp, vp]
+    lib.bfCudaGmresScale.restype = i32
     lib.bfCudaAbiVersion.argtypes = []
     lib.bfCudaAbiVersion.restype = i32
     if path is None:

@@ -127,6 +127,88 @@ __global__ void gmresCombine(const double2 *V, long long n, const double2 *y, in
   }
 }
 
+// ---- building blocks of the ROW-DISTRIBUTED solve (butterfly_b200/gmres.py) -------------------------
+// Every rank holds its rows of the Krylov basis; a Gram-Schmidt pass is "local partial sums -> one
+// all_reduce -> local update".  These kernels are the local halves: all projections of a pass in ONE
+// sweep over the work vector, fixed-order two-stage sums (bitwise reproducible run to run).
+constexpr int kProjChunk = 8;
+
+// partials[(c) * gridDim.x + b] = sum over block b's elements of conj(V[c]) * w, c < mc;
+// if normSlot >= 0 also partials[normSlot * gridDim.x + b] = sum |w|^2.
+__global__ void __launch_bounds__(kThreads) gmresProjectPartial(const double2 *__restrict__ V, long long ldv, int mc,
+                                                                 const double2 *__restrict__ w, long long n,
+                                                                 double2 *__restrict__ partials, int normSlot) {
+  __shared__ double2 sh[kThreads / 32];
+  double2 acc[kProjChunk];
+  double nrm = 0.0;
+#pragma unroll
+  for (int c = 0; c < kProjChunk; ++c) acc[c] = make_double2(0.0, 0.0);
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    const double2 b = w[k];
+    nrm += b.x * b.x + b.y * b.y;
+#pragma unroll
+    for (int c = 0; c < kProjChunk; ++c)
+      if (c < mc) {
+        const double2 a = V[(long long)c * ldv + k];
+        acc[c].x += a.x * b.x + a.y * b.y;
+        acc[c].y += a.x * b.y - a.y * b.x;
+      }
+  }
+#pragma unroll
+  for (int c = 0; c < kProjChunk; ++c)
+    if (c < mc) {
+      const double2 t = blockSum(acc[c], sh);
+      if (threadIdx.x == 0) partials[(long long)c * gridDim.x + blockIdx.x] = t;
+    }
+  if (normSlot >= 0) {
+    const double2 t = blockSum(make_double2(nrm, 0.0), sh);
+    if (threadIdx.x == 0) partials[(long long)normSlot * gridDim.x + blockIdx.x] = t;
+  }
+}
+
+// out[i] = sum_b partials[i * num + b], one block per output, fixed order
+__global__ void __launch_bounds__(kThreads) gmresFinalize(const double2 *__restrict__ partials, int num, double2 *__restrict__ out) {
+  __shared__ double2 sh[kThreads / 32];
+  const double2 t = totalOf(partials + (long long)blockIdx.x * num, num, sh);
+  if (threadIdx.x == 0) out[blockIdx.x] = t;
+}
+
+// w -= sum_{i<m} h[i] V[i];  partials[b] = sum |w_new|^2 over block b
+__global__ void __launch_bounds__(kThreads) gmresSubtractPartial(const double2 *__restrict__ V, long long ldv, int m,
+                                                                  const double2 *__restrict__ h, double2 *__restrict__ w,
+                                                                  long long n, double2 *__restrict__ partials) {
+  __shared__ double2 sh[kThreads / 32];
+  extern __shared__ double2 hs[];
+  for (int i = threadIdx.x; i < m; i += kThreads) hs[i] = h[i];
+  __syncthreads();
+  double nrm = 0.0;
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    double2 b = w[k];
+#pragma unroll 4
+    for (int i = 0; i < m; ++i) {
+      const double2 a = V[(long long)i * ldv + k], c = hs[i];
+      b.x -= c.x * a.x - c.y * a.y;
+      b.y -= c.x * a.y + c.y * a.x;
+    }
+    w[k] = b;
+    nrm += b.x * b.x + b.y * b.y;
+  }
+  const double2 t = blockSum(make_double2(nrm, 0.0), sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+// dst = w / sqrt(nrm2->x)  (and dst2, when given: the all_gather staging copy)
+__global__ void __launch_bounds__(kThreads) gmresScale(const double2 *__restrict__ w, long long n, const double2 *__restrict__ nrm2,
+                                                        double2 *__restrict__ dst, double2 *__restrict__ dst2) {
+  const double nrm = sqrt(nrm2->x);
+  for (long long k = (long long)blockIdx.x * kThreads + threadIdx.x; k < n; k += (long long)gridDim.x * kThreads) {
+    const double2 a = w[k];
+    const double2 r = make_double2(a.x / nrm, a.y / nrm);
+    dst[k] = r;
+    if (dst2) dst2[k] = r;
+  }
+}
+
 using cplx = std::complex<double>;
 struct Givens { cplx c, s; };
 // src/vec_complex.c:276-287
@@ -247,4 +329,40 @@ done:
   cudaFree(V); cudaFree(w); cudaFree(partials); cudaFree(hcol); cudaFree(dx0); cudaFree(dy);
   if (prevDev >= 0 && prevDev != info.device) cudaSetDevice(prevDev);
   return st;
+}
+
+// ---- C ABI of the row-distributed building blocks (device pointers, caller's stream) ------------------
+extern "C" int64_t bfCudaGmresScratchBytes(int64_t m) { return (int64_t)sizeof(double2) * kBlocks * (m + 2); }
+
+extern "C" BfCudaStatus bfCudaGmresProject(const void *V, int64_t ldv, int64_t m, const void *w, int64_t n, void *out,
+                                           void *scratch, void *stream) {
+  if (m < 0 || n < 0 || !w || !out || !scratch || (m > 0 && !V)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  cudaStream_t s = (cudaStream_t)stream;
+  double2 *part = (double2 *)scratch;
+  const double2 *Vd = (const double2 *)V;
+  // chunks of kProjChunk basis vectors per sweep; the last sweep also sums |w|^2 into slot m
+  for (int64_t i0 = 0; i0 == 0 || i0 < m; i0 += kProjChunk) {
+    const int mc = (int)std::min<int64_t>(kProjChunk, m - i0);
+    const bool last = i0 + kProjChunk >= m;
+    gmresProjectPartial<<<kBlocks, kThreads, 0, s>>>(Vd ? Vd + i0 * ldv : nullptr, ldv, mc, (const double2 *)w, n,
+                                                     part + i0 * kBlocks, last ? mc : -1);
+  }
+  gmresFinalize<<<(unsigned)(m + 1), kThreads, 0, s>>>(part, kBlocks, (double2 *)out);
+  return cudaGetLastError() == cudaSuccess ? BF_CUDA_OK : BF_CUDA_ERROR_RUNTIME;
+}
+
+extern "C" BfCudaStatus bfCudaGmresSubtract(const void *V, int64_t ldv, int64_t m, const void *h, void *w, int64_t n,
+                                            void *nrm2Out, void *scratch, void *stream) {
+  if (m < 0 || n < 0 || !w || !nrm2Out || !scratch || (m > 0 && (!V || !h))) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  cudaStream_t s = (cudaStream_t)stream;
+  gmresSubtractPartial<<<kBlocks, kThreads, (size_t)std::max<int64_t>(m, 1) * sizeof(double2), s>>>(
+      (const double2 *)V, ldv, (int)m, (const double2 *)h, (double2 *)w, n, (double2 *)scratch);
+  gmresFinalize<<<1, kThreads, 0, s>>>((const double2 *)scratch, kBlocks, (double2 *)nrm2Out);
+  return cudaGetLastError() == cudaSuccess ? BF_CUDA_OK : BF_CUDA_ERROR_RUNTIME;
+}
+
+extern "C" BfCudaStatus bfCudaGmresScale(const void *w, int64_t n, const void *nrm2, void *dst, void *dst2, void *stream) {
+  if (n < 0 || !w || !nrm2 || !dst) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  gmresScale<<<kBlocks, kThreads, 0, (cudaStream_t)stream>>>((const double2 *)w, n, (const double2 *)nrm2, (double2 *)dst, (double2 *)dst2);
+  return cudaGetLastError() == cudaSuccess ? BF_CUDA_OK : BF_CUDA_ERROR_RUNTIME;
 }

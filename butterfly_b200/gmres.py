@@ -8,15 +8,18 @@ needs (the operand of the next apply) is all_gathered from the row owners.
 
 orthogonalization="mgs" follows the reference step for step (j + 2 scalar all_reduces in iteration j);
 "cgs" projects against all basis vectors at once (2 all_reduces per iteration, the north star's count)
-at the price of classical Gram-Schmidt's weaker orthogonality.
+at the price of classical Gram-Schmidt's weaker orthogonality; "cgs2" repeats that pass once (4
+all_reduces), which restores orthogonality to working precision.
 
-torch is plumbing here (device vectors, torch.distributed); the operator applies are the hand-written
-stage kernels behind RowShardedOperator.apply.  The single-GPU, fully fused variant is
-bfCudaSolveGMRES (csrc/bf_gmres.cu).
+On CUDA tensors the local halves of every pass are the kernels of csrc/bf_gmres.cu
+(bfCudaGmresProject / Subtract / Scale: all projections of a pass in one sweep, fixed-order sums) and
+torch is plumbing only (buffers, all_reduce / all_gather over NCCL).  On CPU tensors (the gloo tests of
+the host logic) the same steps are spelled with torch ops.  The single-GPU, fully fused variant is
+bfCudaSolveGMRES.
 """
 from __future__ import annotations
 
-import cmath
+import ctypes as C
 import math
 
 
@@ -38,6 +41,42 @@ def _rot(c, s, z0, z1):
     return c.conjugate() * z0 - s * z1, s * z0 + c * z1
 
 
+class _NativeGramSchmidt:
+    """The CUDA halves of a Gram-Schmidt pass on this rank's rows (csrc/bf_gmres.cu)."""
+
+    def __init__(self, V, max_iter):
+        import torch
+
+        from . import capi
+
+        self.lib = capi.load_library()
+        self.check = capi.check
+        dev = V.device
+        self.V, self.nloc = V, V.shape[1]
+        self.scratch = torch.empty(int(self.lib.bfCudaGmresScratchBytes(max_iter + 1)), dtype=torch.uint8, device=dev)
+        self.h = torch.zeros(max_iter + 3, dtype=V.dtype, device=dev)    # projections (+ |w|^2 slot)
+        self.h2 = torch.zeros(max_iter + 3, dtype=V.dtype, device=dev)   # second pass of cgs2
+        self.nrm2 = torch.zeros(1, dtype=V.dtype, device=dev)
+        self.stream = lambda: C.c_void_p(torch.cuda.current_stream(dev).cuda_stream or 1)
+
+    def _ptr(self, t, offset=0):
+        return C.c_void_p(t.data_ptr() + 16 * offset)
+
+    def project(self, first, m, w, out, out_offset=0):
+        """out[out_offset + i] = <V[first + i], w> (local part), i < m; out[out_offset + m] = |w|^2 (local)."""
+        self.check(self.lib.bfCudaGmresProject(self._ptr(self.V, first * self.nloc), self.nloc, m, self._ptr(w), self.nloc,
+                                               self._ptr(out, out_offset), self._ptr(self.scratch), self.stream()), "bfCudaGmresProject")
+
+    def subtract(self, first, m, h, h_offset, w):
+        """w -= sum_i h[h_offset + i] V[first + i]; nrm2 = |w|^2 (local part)."""
+        self.check(self.lib.bfCudaGmresSubtract(self._ptr(self.V, first * self.nloc), self.nloc, m, self._ptr(h, h_offset), self._ptr(w),
+                                                self.nloc, self._ptr(self.nrm2), self._ptr(self.scratch), self.stream()), "bfCudaGmresSubtract")
+
+    def scale(self, w, dst, dst2=None):
+        self.check(self.lib.bfCudaGmresScale(self._ptr(w), self.nloc, self._ptr(self.nrm2), self._ptr(dst),
+                                             self._ptr(dst2) if dst2 is not None else None, self.stream()), "bfCudaGmresScale")
+
+
 def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, orthogonalization: str = "mgs"):
     """Solve A x = b with A = `op` (RowShardedOperator), b replicated on every rank (torch tensor of n
     complex entries on the operator's device).  Returns (x_full, num_iter, rel_residual, num_applies);
@@ -45,12 +84,20 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
     import torch
     import torch.distributed as dist
 
+    if orthogonalization not in ("mgs", "cgs", "cgs2"):
+        raise ValueError(f"orthogonalization = {orthogonalization!r}")
     world = op.world
     r0, r1 = op.y_range
+    nloc = r1 - r0
     n = b.numel()
     dev, dt = b.device, b.dtype
     b = b.reshape(n, 1)
     ybuf = torch.zeros(n, 1, dtype=dt, device=dev)
+    xfull = torch.zeros(n, 1, dtype=dt, device=dev)
+    equal_rows = all(op.y_cuts[i + 1] - op.y_cuts[i] == nloc for i in range(world))
+    native = b.is_cuda
+    if native and dt != torch.complex128:
+        raise TypeError("the CUDA Gram-Schmidt kernels are complex128")
 
     def allsum(t):
         if world > 1:
@@ -59,8 +106,12 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
         return t
 
     def full_from_local(v_loc):
+        """Every rank's rows of a distributed vector -> the replicated operand of the next apply."""
         if world == 1:
             return v_loc.reshape(n, 1)
+        if equal_rows:
+            dist.all_gather_into_tensor(torch.view_as_real(xfull).reshape(-1), torch.view_as_real(v_loc.contiguous()).reshape(-1), group=op.group)
+            return xfull
         ybuf[r0:r1, 0] = v_loc
         return op.gather_rows(ybuf)
 
@@ -73,7 +124,8 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
     else:
         r_loc = b[r0:r1, 0].clone()
     beta = math.sqrt(float(allsum((r_loc.conj() * r_loc).real.sum().reshape(1))[0]))
-    V = torch.empty(max_iter + 1, r1 - r0, dtype=dt, device=dev)
+    V = torch.empty(max_iter + 1, nloc, dtype=dt, device=dev)
+    gs = _NativeGramSchmidt(V, max_iter) if native else None
     H = [[0j] * (max_iter + 1) for _ in range(max_iter)]
     S = [0j] * (max_iter + 1)
     S[0] = beta + 0j
@@ -84,21 +136,46 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
     while j < max_iter and not converged:
         op.apply(full_from_local(V[j]).contiguous(), ybuf)  # W = A V[j], src/linalg.c:155
         applies += 1
-        w = ybuf[r0:r1, 0].clone()
-        hcol = torch.zeros(j + 2, dtype=dt, device=dev)
-        if orthogonalization == "mgs":  # src/linalg.c:172-186
-            for i in range(j + 1):
-                h = allsum(torch.vdot(V[i], w).reshape(1))
-                hcol[i] = h[0]
-                w -= h[0] * V[i]
+        m = j + 1
+        if native:
+            w = ybuf[r0:r1, 0]  # orthogonalised in place; the next apply overwrites it
+            if orthogonalization == "mgs":  # src/linalg.c:172-186, one all_reduce per basis vector
+                for i in range(m):
+                    gs.project(i, 1, w, gs.h, i)
+                    allsum(gs.h[i:i + 1])
+                    gs.subtract(i, 1, gs.h, i, w)
+                hdev = gs.h[:m]
+            else:
+                gs.project(0, m, w, gs.h)
+                allsum(gs.h[:m])
+                gs.subtract(0, m, gs.h, 0, w)
+                hdev = gs.h[:m]
+                if orthogonalization == "cgs2":
+                    gs.project(0, m, w, gs.h2)
+                    allsum(gs.h2[:m])
+                    gs.subtract(0, m, gs.h2, 0, w)
+                    hdev = gs.h[:m] + gs.h2[:m]
+            allsum(gs.nrm2)
+            gs.scale(w, V[j + 1])
+            host = torch.cat([hdev, gs.nrm2]).cpu().tolist()  # the one host sync of the iteration
+            hh = [complex(v) for v in host[:m]] + [complex(math.sqrt(host[m].real))]
         else:
-            h = allsum(V[: j + 1].conj() @ w)
-            hcol[: j + 1] = h
-            w -= V[: j + 1].T @ h
-        nrm = torch.sqrt(allsum((w.conj() * w).real.sum().reshape(1)))
-        hcol[j + 1] = nrm[0]
-        V[j + 1] = w / nrm[0]
-        hh = [complex(v) for v in hcol.cpu().tolist()]
+            w = ybuf[r0:r1, 0].clone()
+            hcol = torch.zeros(j + 2, dtype=dt, device=dev)
+            if orthogonalization == "mgs":
+                for i in range(m):
+                    h = allsum(torch.vdot(V[i], w).reshape(1))
+                    hcol[i] = h[0]
+                    w -= h[0] * V[i]
+            else:
+                for _ in range(2 if orthogonalization == "cgs2" else 1):
+                    h = allsum(V[:m].conj() @ w)
+                    hcol[:m] += h
+                    w -= V[:m].T @ h
+            nrm = torch.sqrt(allsum((w.conj() * w).real.sum().reshape(1)))
+            hcol[j + 1] = nrm[0]
+            V[j + 1] = w / nrm[0]
+            hh = [complex(v) for v in hcol.cpu().tolist()]
         for i in range(j):
             hh[i], hh[i + 1] = _rot(J[i][0], J[i][1], hh[i], hh[i + 1])
         c, s = _givens(hh[j], hh[j + 1])
@@ -118,7 +195,7 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
         for c_ in range(r + 1, j):
             acc -= H[c_][r] * y[c_]
         y[r] = acc / H[r][r]
-    x_loc = torch.zeros(r1 - r0, dtype=dt, device=dev)
+    x_loc = torch.zeros(nloc, dtype=dt, device=dev)
     if j > 0:
         x_loc = V[:j].T @ torch.tensor(y[:j], dtype=dt, device=dev)
     if x0 is not None:

@@ -213,6 +213,22 @@ BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, d
                               int64_t maxNumIter, void *x, int64_t *numIter, double *relResidual,
                               int64_t *numApplies);
 
+/* Local halves of a Gram-Schmidt pass for a solve whose Krylov basis is distributed by rows over
+ * several GPUs (butterfly_b200/gmres.py; the caller all_reduces `out` / `nrm2Out` between them).
+ * All pointers are DEVICE pointers to complex doubles, `stream` a cudaStream_t, `scratch` at least
+ * bfCudaGmresScratchBytes(m) bytes.  Sums are two-stage in a fixed order (bitwise reproducible).
+ *   Project : out[i] = sum_k conj(V[i*ldv + k]) w[k], i < m (zdotc as src/mat_dense_complex.c:115-121);
+ *             out[m] = (sum_k |w[k]|^2, 0)
+ *   Subtract: w -= sum_{i<m} h[i] V[i];  nrm2Out[0] = (sum_k |w_new[k]|^2, 0)   (src/linalg.c:172-190)
+ *   Scale   : dst = w / sqrt(nrm2[0].re), also written to dst2 when non-NULL      (src/linalg.c:196-202) */
+int64_t bfCudaGmresScratchBytes(int64_t m);
+BfCudaStatus bfCudaGmresProject(const void *V, int64_t ldv, int64_t m, const void *w, int64_t n,
+                                void *out, void *scratch, void *stream);
+BfCudaStatus bfCudaGmresSubtract(const void *V, int64_t ldv, int64_t m, const void *h, void *w,
+                                 int64_t n, void *nrm2Out, void *scratch, void *stream);
+BfCudaStatus bfCudaGmresScale(const void *w, int64_t n, const void *nrm2, void *dst, void *dst2,
+                              void *stream);
+
 /* Number of kernel launches the last apply on this plan issued (bench.py's gpu_launches). */
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *plan);
 
