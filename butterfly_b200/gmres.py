@@ -109,11 +109,11 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
         """Every rank's rows of a distributed vector -> the replicated operand of the next apply."""
         if world == 1:
             return v_loc.reshape(n, 1)
-        if equal_rows:
+        if equal_rows and native:
             dist.all_gather_into_tensor(torch.view_as_real(xfull).reshape(-1), torch.view_as_real(v_loc.contiguous()).reshape(-1), group=op.group)
             return xfull
         ybuf[r0:r1, 0] = v_loc
-        return op.gather_rows(ybuf)
+        return op.gather_rows(ybuf, out=xfull)
 
     applies = 0
     if x0 is not None:

@@ -400,23 +400,37 @@ class RowShardedOperator:
         be.end()
         return y
 
-    def gather_rows(self, y):
-        """Full result on every rank: all_gather of the owned row ranges (padded to the longest)."""
+    def gather_rows(self, y, out=None):
+        """Full result on every rank: one all_gather of the owned row ranges (padded to the longest when
+        the ranges differ) through persistent staging buffers."""
         import torch
         import torch.distributed as dist
 
+        if out is None:
+            out = torch.empty_like(y)
+        if self.world == 1:
+            out.copy_(y)
+            return out
         r0, r1 = self.y_range
-        width = max(self.y_cuts[i + 1] - self.y_cuts[i] for i in range(self.world))
-        pad = torch.zeros((width, y.shape[1]), dtype=y.dtype, device=y.device)
-        pad[: r1 - r0] = y[r0:r1]
-        pv = torch.view_as_real(pad) if pad.is_complex() else pad
-        parts = [torch.empty_like(pv) for _ in range(self.world)]
-        dist.all_gather(parts, pv.contiguous(), group=self.group)
-        out = torch.empty_like(y)
+        nrhs = y.shape[1]
+        widths = [self.y_cuts[i + 1] - self.y_cuts[i] for i in range(self.world)]
+        width = max(widths)
+        real = lambda t: (torch.view_as_real(t) if t.is_complex() else t).reshape(-1)
+        if min(widths) == width and y.is_contiguous() and out.is_contiguous():
+            dist.all_gather_into_tensor(real(out), real(y[r0:r1]), group=self.group)  # no staging at all
+            return out
+        key = (y.device, y.dtype, nrhs)
+        if not hasattr(self, "_gather_bufs"):
+            self._gather_bufs = {}
+        if key not in self._gather_bufs:
+            self._gather_bufs[key] = (torch.zeros((width, nrhs), dtype=y.dtype, device=y.device),
+                                      torch.empty((self.world * width, nrhs), dtype=y.dtype, device=y.device))
+        pad_in, pad_out = self._gather_bufs[key]
+        pad_in[: r1 - r0] = y[r0:r1]
+        dist.all_gather_into_tensor(real(pad_out), real(pad_in), group=self.group)
         for i in range(self.world):
             a, b = self.y_cuts[i], self.y_cuts[i + 1]
-            p = torch.view_as_complex(parts[i]) if y.is_complex() else parts[i]
-            out[a:b] = p[: b - a]
+            out[a:b] = pad_out[i * width: i * width + (b - a)]
         return out
 
 
