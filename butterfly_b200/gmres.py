@@ -133,11 +133,38 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
     residual, converged, j = 0.0, not beta > 0.0, 0
     if beta > 0.0:
         V[0] = r_loc / beta
-    while j < max_iter and not converged:
-        op.apply(full_from_local(V[j]).contiguous(), ybuf)  # W = A V[j], src/linalg.c:155
-        applies += 1
-        m = j + 1
-        if native:
+    def close_column(jj, hh):
+        """Rotations, new Givens pair, rotated right-hand side for Hessenberg column jj (src/linalg.c:206-231);
+        True when the residual test fires (the reference then leaves the loop without counting jj)."""
+        nonlocal residual
+        for i in range(jj):
+            hh[i], hh[i + 1] = _rot(J[i][0], J[i][1], hh[i], hh[i + 1])
+        c, s = _givens(hh[jj], hh[jj + 1])
+        J.append((c, s))
+        hh[jj], hh[jj + 1] = _rot(c, s, hh[jj], hh[jj + 1])
+        S[jj], S[jj + 1] = _rot(c, s, S[jj], S[jj + 1])
+        for i in range(jj + 1):
+            H[jj][i] = hh[i]
+        residual = abs(S[jj + 1]) / beta
+        return residual < tol
+
+    if native:
+        # The Hessenberg column of iteration j is read on the host while the GPU already runs iteration
+        # j + 1 (the host never drains the queue); a convergence found one iteration late costs one
+        # discarded apply and changes nothing in the result.
+        pin = torch.empty(2, max_iter + 2, dtype=dt).pin_memory()
+        events = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def read_column(jj):
+            events[jj & 1].synchronize()
+            host = pin[jj & 1, : jj + 2].tolist()
+            return [complex(v) for v in host[: jj + 1]] + [complex(math.sqrt(host[jj + 1].real))]
+
+        pending = None
+        while j < max_iter and not converged:
+            op.apply(full_from_local(V[j]).contiguous(), ybuf)  # W = A V[j], src/linalg.c:155
+            applies += 1
+            m = j + 1
             w = ybuf[r0:r1, 0]  # orthogonalised in place; the next apply overwrites it
             if orthogonalization == "mgs":  # src/linalg.c:172-186, one all_reduce per basis vector
                 for i in range(m):
@@ -157,35 +184,35 @@ def solve_gmres_sharded(op, b, x0=None, tol: float = 1e-12, max_iter: int = 50, 
                     hdev = gs.h[:m] + gs.h2[:m]
             allsum(gs.nrm2)
             gs.scale(w, V[j + 1])
-            host = torch.cat([hdev, gs.nrm2]).cpu().tolist()  # the one host sync of the iteration
-            hh = [complex(v) for v in host[:m]] + [complex(math.sqrt(host[m].real))]
+            pin[j & 1, : m + 1].copy_(torch.cat([hdev, gs.nrm2]), non_blocking=True)
+            events[j & 1].record()
+            if pending is not None and close_column(pending, read_column(pending)):
+                converged, j = True, pending
+                break
+            pending = j
+            j += 1
+        if not converged and pending is not None and close_column(pending, read_column(pending)):
+            converged, j = True, pending
+    while not native and j < max_iter and not converged:
+        op.apply(full_from_local(V[j]).contiguous(), ybuf)
+        applies += 1
+        m = j + 1
+        w = ybuf[r0:r1, 0].clone()
+        hcol = torch.zeros(j + 2, dtype=dt, device=dev)
+        if orthogonalization == "mgs":
+            for i in range(m):
+                h = allsum(torch.vdot(V[i], w).reshape(1))
+                hcol[i] = h[0]
+                w -= h[0] * V[i]
         else:
-            w = ybuf[r0:r1, 0].clone()
-            hcol = torch.zeros(j + 2, dtype=dt, device=dev)
-            if orthogonalization == "mgs":
-                for i in range(m):
-                    h = allsum(torch.vdot(V[i], w).reshape(1))
-                    hcol[i] = h[0]
-                    w -= h[0] * V[i]
-            else:
-                for _ in range(2 if orthogonalization == "cgs2" else 1):
-                    h = allsum(V[:m].conj() @ w)
-                    hcol[:m] += h
-                    w -= V[:m].T @ h
-            nrm = torch.sqrt(allsum((w.conj() * w).real.sum().reshape(1)))
-            hcol[j + 1] = nrm[0]
-            V[j + 1] = w / nrm[0]
-            hh = [complex(v) for v in hcol.cpu().tolist()]
-        for i in range(j):
-            hh[i], hh[i + 1] = _rot(J[i][0], J[i][1], hh[i], hh[i + 1])
-        c, s = _givens(hh[j], hh[j + 1])
-        J.append((c, s))
-        hh[j], hh[j + 1] = _rot(c, s, hh[j], hh[j + 1])
-        S[j], S[j + 1] = _rot(c, s, S[j], S[j + 1])
-        for i in range(j + 1):
-            H[j][i] = hh[i]
-        residual = abs(S[j + 1]) / beta
-        if residual < tol:  # the reference leaves the loop before counting this column
+            for _ in range(2 if orthogonalization == "cgs2" else 1):
+                h = allsum(V[:m].conj() @ w)
+                hcol[:m] += h
+                w -= V[:m].T @ h
+        nrm = torch.sqrt(allsum((w.conj() * w).real.sum().reshape(1)))
+        hcol[j + 1] = nrm[0]
+        V[j + 1] = w / nrm[0]
+        if close_column(j, [complex(v) for v in hcol.cpu().tolist()]):
             converged = True
             break
         j += 1
