@@ -241,13 +241,31 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
   });
 
   // ---- 5. items and tiles per stage -------------------------------------------------------------
-  const int R = maxItemRows(desc.dtype);
+  // An item is read by ONE warp (1-RHS kernel), so an item much longer than a queue's share of its
+  // stage is a tail nobody can help with.  Operators that fill the GPU many times over never see
+  // this; on small ones (N ~ 16k: 170 KB per queue, but 32 rows of a first-level block are 700 KB)
+  // it tripled the stage time.  Items whose rows are long are therefore cut into fewer rows (down
+  // to 8, one DMMA fragment) so that an item stays near the per-queue share.
+  const int Rmax = maxItemRows(desc.dtype);
+  const int64_t esBytes = desc.dtype == BF_CUDA_COMPLEX_F64 ? 16 : 8;
+  std::vector<int64_t> stageBytes(D.stages.size(), 0);
+  for (const Frag &fr : frags)
+    if (fr.seq >= 0 && D.ops[(size_t)fr.seq].kind == BF_CUDA_LEAF_DENSE)
+      stageBytes[(size_t)fr.stage] += elems[(size_t)fr.elem].len * D.ops[(size_t)fr.seq].k * esBytes;
   for (size_t f = 0; f < frags.size();) {
     size_t f1 = f;
     while (f1 < frags.size() && frags[f1].stage == frags[f].stage && frags[f1].elem == frags[f].elem) ++f1;
     const Elem &el = elems[(size_t)frags[f].elem];
     Stage &S = D.stages[(size_t)frags[f].stage];
     const bool zeroOnly = frags[f].seq < 0;
+    int R = Rmax;
+    if (!zeroOnly && el.len > 8) {
+      int64_t rowBytes = 0;
+      for (size_t q = f; q < f1; ++q)
+        if (D.ops[(size_t)frags[q].seq].kind == BF_CUDA_LEAF_DENSE) rowBytes += D.ops[(size_t)frags[q].seq].k * esBytes;
+      const int64_t share = stageBytes[(size_t)frags[f].stage] / std::max(numQueues, 1);
+      while (R > 8 && (int64_t)R * rowBytes > share) R -= 8;
+    }
     const int64_t nChunks = (el.len + R - 1) / R;
     for (int64_t c = 0; c < nChunks; ++c) {
       // cut at multiples of 8 rows (whole m8 DMMA fragments); only the last chunk is ragged

@@ -49,12 +49,17 @@ def test_queue_count_does_not_change_the_result():
     raw = synth.random_hodbf(n=1024, dtype=capi.COMPLEX_F64, seed=9)
     x = _x(np.random.default_rng(1), raw.num_cols, 1, True)
     ys = []
-    for q in (1, 8, 1184):
+    for q in (1, 2, 8, 1184):
         t = Tables(raw, capi.OP_N, num_queues=q)
         t.check_queues()
         ys.append(t.apply(x))
         t.close()
-    assert np.array_equal(ys[0], ys[1]) and np.array_equal(ys[0], ys[2])
+    # dealing the same items to more queues changes nothing, bit for bit ...
+    assert np.array_equal(ys[0], ys[1])
+    # ... and when a queue's share gets small enough that long items are cut into fewer rows (other
+    # tile shapes, another summation order) the result moves by rounding only
+    for y in ys[2:]:
+        assert np.linalg.norm(y - ys[0]) <= 1e-14 * np.linalg.norm(ys[0])
 
 
 def test_oracle_transpose_is_adjoint():
