@@ -165,6 +165,7 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanGetWorkspace",
     "bfCudaPlanGetWorkspaceLayout",
     "bfCudaSolveGMRES",
+    "bfCudaSolveGMRESPrecond",
     "bfCudaGmresScratchBytes",
     "bfCudaGmresProject",
     "bfCudaGmresSubtract",

@@ -253,17 +253,36 @@ BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *out
 /* bfSolveGMRES (src/linalg.c:47) with the Krylov basis resident on the GPU.  Same signature, same
  * ownership (a non-NULL X0 is consumed: the reference deletes it before returning,
  * src/linalg.c:312-313), same *numIter.  A must be attached, B (and X0) n x 1 BfMatDenseComplex with
- * unit column stride, M NULL (the reference's left preconditioner is a host LU solve); anything else
- * raises BF_ERROR_NOT_IMPLEMENTED like an unimplemented vtable slot would. */
+ * unit column stride.  A non-NULL M is the reference's left preconditioner: bfMatSolve(M, .) runs on
+ * the host exactly as in the reference (src/linalg.c:131,159 — block LU solves in the examples), the
+ * vector crossing PCIe once each way per iteration.  Anything else raises BF_ERROR_NOT_IMPLEMENTED like
+ * an unimplemented vtable slot would. */
+static int solveWithM(void *ctx, const void *in, void *out, int64_t n) {
+  BfMat const *M = ctx;
+  BfMatDenseComplex *W = bfMatDenseComplexNewViewFromPtr((BfSize)n, 1, (BfComplex *)in);
+  BfMat *Wm = bfMatDenseComplexToMat(W);
+  BfMat *Z = bfMatSolve(M, Wm);
+  bfMatDelete(&Wm);
+  if (Z == NULL) return 1;
+  int bad = bfMatGetType(Z) != BF_TYPE_MAT_DENSE_COMPLEX || bfMatGetNumRows(Z) != (BfSize)n || bfMatGetNumCols(Z) != 1;
+  if (!bad) {
+    BfMatDenseComplex const *Zd = bfMatConstToMatDenseComplexConst(Z);
+    for (int64_t i = 0; i < n; ++i) ((BfComplex *)out)[i] = Zd->data[(BfSize)i * Zd->rowStride];
+  }
+  bfMatDelete(&Z);
+  return bad;
+}
+
 BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol, BfSize maxNumIter,
                            BfSize *numIter, BfMat const *M) {
-  if (!isAttached(A) || M != NULL || bfMatGetType(B) != BF_TYPE_MAT_DENSE_COMPLEX ||
+  if (!isAttached(A) || bfMatGetType(B) != BF_TYPE_MAT_DENSE_COMPLEX ||
       (X0 != NULL && bfMatGetType(X0) != BF_TYPE_MAT_DENSE_COMPLEX) || bfMatGetNumCols(B) != 1) {
     bfSetError(BF_ERROR_NOT_IMPLEMENTED);
     return NULL;
   }
   if (maxNumIter == 0 || bfMatGetNumRows(A) != bfMatGetNumCols(A) || bfMatGetNumRows(B) != bfMatGetNumRows(A) ||
-      (X0 != NULL && (bfMatGetNumRows(X0) != bfMatGetNumRows(A) || bfMatGetNumCols(X0) != 1))) {
+      (X0 != NULL && (bfMatGetNumRows(X0) != bfMatGetNumRows(A) || bfMatGetNumCols(X0) != 1)) ||
+      (M != NULL && (bfMatGetNumRows(M) != bfMatGetNumRows(A) || bfMatGetNumCols(M) != bfMatGetNumRows(A)))) {
     bfSetError(BF_ERROR_INVALID_ARGUMENTS); /* src/linalg.c:80-110 */
     return NULL;
   }
@@ -279,7 +298,10 @@ BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol
   BfMatDenseComplex *X = bfMatDenseComplexNew();
   bfMatDenseComplexInit(X, n, 1);
   int64_t it = 0;
-  BfCudaStatus st = bfCudaSolveGMRES(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL, NULL);
+  BfCudaStatus st = M == NULL
+                        ? bfCudaSolveGMRES(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL, NULL)
+                        : bfCudaSolveGMRESPrecond(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL,
+                                                  NULL, solveWithM, (void *)M);
   free(b);
   free(x0);
   if (X0 != NULL) bfMatDelete(&X0);

@@ -233,8 +233,8 @@ void applyGivens(const Givens &g, cplx &z0, cplx &z1) {
     if (e_ != cudaSuccess) { st = e_ == cudaErrorMemoryAllocation ? BF_CUDA_ERROR_OUT_OF_MEMORY : BF_CUDA_ERROR_RUNTIME; goto done; } \
   } while (0)
 
-extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, double tol, int64_t maxNumIter,
-                                         void *x, int64_t *numIter, double *relResidual, int64_t *numApplies) {
+static BfCudaStatus solveImpl(BfCudaPlan *plan, const void *b, const void *x0, double tol, int64_t maxNumIter, void *x,
+                              int64_t *numIter, double *relResidual, int64_t *numApplies, BfCudaPrecondFn precond, void *precondCtx) {
   if (!plan || !b || !x || maxNumIter <= 0) return BF_CUDA_ERROR_INVALID_ARGUMENT; // src/linalg.c:80-81
   BfCudaPlanInfo info;
   BfCudaStatus st = bfCudaPlanGetInfo(plan, &info);
@@ -250,6 +250,18 @@ extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const 
   double2 *V = nullptr, *w = nullptr, *partials = nullptr, *hcol = nullptr, *dx0 = nullptr, *dy = nullptr;
   std::vector<cplx> S((size_t)m + 1, cplx(0)), hhost((size_t)m + 2), Hall((size_t)m * ((size_t)m + 1), cplx(0));
   std::vector<Givens> J;
+  std::vector<cplx> hostIn, hostOut; // left preconditioner: the vector crosses PCIe once each way
+  if (precond) { hostIn.resize((size_t)n); hostOut.resize((size_t)n); }
+  // w <- M^{-1} w through the caller's host routine (the reference: bfMatSolve(M, W), src/linalg.c:131,159)
+  auto applyPrecond = [&](double2 *w) -> BfCudaStatus {
+    if (cudaMemcpyAsync(hostIn.data(), w, (size_t)n * sizeof(double2), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess)
+      return BF_CUDA_ERROR_RUNTIME;
+    if (precond(precondCtx, hostIn.data(), hostOut.data(), n) != 0) return BF_CUDA_ERROR_RUNTIME;
+    if (cudaMemcpyAsync(w, hostOut.data(), (size_t)n * sizeof(double2), cudaMemcpyHostToDevice, stream) != cudaSuccess)
+      return BF_CUDA_ERROR_RUNTIME;
+    return BF_CUDA_OK;
+  };
   double beta = 0.0, residual = 0.0;
   int64_t applies = 0;
   int j = 0;
@@ -270,6 +282,7 @@ extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const 
     ++applies;
     gmresSub<<<kBlocks, kThreads, 0, stream>>>(w, V, n, w);
   }
+  if (precond) { st = applyPrecond(w); if (st != BF_CUDA_OK) goto done; }
   // beta = ||r||, V[0] = r / beta, S = beta e1 (src/linalg.c:136-148)
   gmresDot<<<kBlocks, kThreads, 0, stream>>>(nullptr, w, n, partials);
   gmresNormalize<<<kBlocks, kThreads, 0, stream>>>(partials, kBlocks, w, nullptr, n, V, hcol);
@@ -285,6 +298,7 @@ extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const 
     st = bfCudaApplyDevice(plan, BF_CUDA_OP_N, Vj, 1, 1, w, 1, stream); // W = A V[j] (src/linalg.c:155)
     if (st != BF_CUDA_OK) goto done;
     ++applies;
+    if (precond) { st = applyPrecond(w); if (st != BF_CUDA_OK) goto done; }
     // modified Gram-Schmidt (src/linalg.c:172-186), one kernel per basis vector
     double2 *pIn = partials, *pOut = partials + kBlocks;
     gmresDot<<<kBlocks, kThreads, 0, stream>>>(V, w, n, pIn);
@@ -329,6 +343,17 @@ done:
   cudaFree(V); cudaFree(w); cudaFree(partials); cudaFree(hcol); cudaFree(dx0); cudaFree(dy);
   if (prevDev >= 0 && prevDev != info.device) cudaSetDevice(prevDev);
   return st;
+}
+
+extern "C" BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, double tol, int64_t maxNumIter,
+                                         void *x, int64_t *numIter, double *relResidual, int64_t *numApplies) {
+  return solveImpl(plan, b, x0, tol, maxNumIter, x, numIter, relResidual, numApplies, nullptr, nullptr);
+}
+
+extern "C" BfCudaStatus bfCudaSolveGMRESPrecond(BfCudaPlan *plan, const void *b, const void *x0, double tol,
+                                                int64_t maxNumIter, void *x, int64_t *numIter, double *relResidual,
+                                                int64_t *numApplies, BfCudaPrecondFn precond, void *precondCtx) {
+  return solveImpl(plan, b, x0, tol, maxNumIter, x, numIter, relResidual, numApplies, precond, precondCtx);
 }
 
 // ---- C ABI of the row-distributed building blocks (device pointers, caller's stream) ------------------

@@ -213,6 +213,17 @@ BfCudaStatus bfCudaSolveGMRES(BfCudaPlan *plan, const void *b, const void *x0, d
                               int64_t maxNumIter, void *x, int64_t *numIter, double *relResidual,
                               int64_t *numApplies);
 
+/* The same solve with a LEFT preconditioner (bfSolveGMRES's `M` argument, src/linalg.c:42-49,131,159):
+ * `precond(ctx, in, out, n)` must write out = M^{-1} in for host arrays of n complex doubles and return
+ * 0.  It is called once for the initial residual and once per iteration, between the apply and the
+ * Gram-Schmidt pass; the vector crosses PCIe once each way per call (the reference's preconditioners
+ * are host LU solves).  relResidual is then the preconditioned residual, as in the reference. */
+typedef int (*BfCudaPrecondFn)(void *ctx, const void *in, void *out, int64_t n);
+BfCudaStatus bfCudaSolveGMRESPrecond(BfCudaPlan *plan, const void *b, const void *x0, double tol,
+                                     int64_t maxNumIter, void *x, int64_t *numIter,
+                                     double *relResidual, int64_t *numApplies, BfCudaPrecondFn precond,
+                                     void *precondCtx);
+
 /* Local halves of a Gram-Schmidt pass for a solve whose Krylov basis is distributed by rows over
  * several GPUs (butterfly_b200/gmres.py; the caller all_reduces `out` / `nrm2Out` between them).
  * All pointers are DEVICE pointers to complex doubles, `stream` a cudaStream_t, `scratch` at least

@@ -62,7 +62,8 @@ BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *out
 
 /* Drop-in for bfSolveGMRES (src/linalg.c:47-49, same signature and ownership) on an attached
  * operator: the Arnoldi process runs on the GPU (bfCudaSolveGMRES) instead of round-tripping every
- * Krylov vector through bfMatMul.  One complex right-hand side, M == NULL. */
+ * Krylov vector through bfMatMul.  One complex right-hand side.  A non-NULL M (left preconditioner) is
+ * applied with the reference's own bfMatSolve(M, .) on the host, once per iteration. */
 BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol, BfSize maxNumIter,
                            BfSize *numIter, BfMat const *M);
 

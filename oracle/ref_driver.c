@@ -15,6 +15,9 @@
 #include <bf/helm2.h>
 #include <bf/layer_pot.h>
 #include <bf/linalg.h>
+#include <bf/lu.h>
+#include <bf/mat_block_diag.h>
+#include <bf/ptr_array.h>
 #include <complex.h>
 #include <bf/mat_coo_complex.h>
 #include <bf/mat_dense_complex.h>
@@ -343,11 +346,47 @@ double refSolveGMRES(BfMat const *A, const double *b, int64_t n, double tol, int
 /* Helpers for calling a bfSolveGMRES-shaped function pointer (the reference's own, or the attach
  * layer's bfCudaSolveGMRESMat) from ctypes on an n x 1 complex right-hand side. */
 typedef BfMat *(*RefGmresFn)(BfMat const *, BfMat const *, BfMat *, BfReal, BfSize, BfSize *, BfMat const *);
+double refCallGMRESPrecond(RefGmresFn fn, BfMat const *A, BfMat const *M, const double *b, int64_t n, double tol, int64_t maxNumIter, double *x, int64_t *numIter);
 double refCallGMRES(RefGmresFn fn, BfMat const *A, const double *b, int64_t n, double tol, int64_t maxNumIter, double *x, int64_t *numIter) {
+  return refCallGMRESPrecond(fn, A, NULL, b, n, tol, maxNumIter, x, numIter);
+}
+
+/* The block Jacobi preconditioner of multiple_scattering_context.c:544-600: LU factorizations of the
+ * diagonal blocks of the dense second-kind matrix K diag(w) + I/2 (tree order), collected as a
+ * MatBlockDiag of bfLuGetMatView objects whose Solve is the LU solve.  `weight` as refHelm2MakeSecondKind. */
+BfMat *refHelm2MakeBlockJacobi(RefHelm2 *h, int64_t numBlocks, double weight) {
+  BfTree *tree = bfQuadtreeToTree(&h->quadtree);
+  BfPerm *revPerm = bfPermGetReversePerm(bfTreeGetPermConst(tree));
+  BfMat *ptsPerm = bfMatCopy(bfMatDenseRealToMat(h->pointsMat));
+  bfMatPermuteRows(ptsPerm, revPerm);
+  BfPoints2 const *pp = bfPoints2ConstViewFromMat(ptsPerm);
+  BfMat *K = bfHelm2GetKernelMatrix(&h->helm, pp, pp, NULL, NULL);
+  BfSize n = bfMatGetNumRows(K);
+  BfMatDenseComplex *Kd = bfMatToMatDenseComplex(K);
+  for (BfSize i = 0; i < n; ++i) {
+    for (BfSize j = 0; j < n; ++j) Kd->data[i * Kd->rowStride + j] *= weight;
+    Kd->data[i * Kd->rowStride + i] += 0.5;
+  }
+  BfPtrArray *blocks = bfPtrArrayNewWithDefaultCapacity();
+  for (int64_t b = 0; b < numBlocks; ++b) {
+    BfSize i0 = n * (BfSize)b / (BfSize)numBlocks, i1 = n * (BfSize)(b + 1) / (BfSize)numBlocks;
+    BfMat *KBlock = bfMatGetBlockView(K, i0, i1, i0, i1);
+    BfLu *lu = bfMatGetLu(KBlock);
+    bfPtrArrayAppend(blocks, bfLuGetMatView(lu));
+    bfMatDelete(&KBlock);
+  }
+  BfMat *M = bfMatBlockDiagToMat(bfMatBlockDiagNewFromBlocks(blocks, BF_POLICY_STEAL));
+  bfMatDelete(&K);
+  bfMatDelete(&ptsPerm);
+  bfPermDeinitAndDealloc(&revPerm);
+  return M; /* leaked by the tests on purpose: the LU objects have no owner to free them through */
+}
+
+double refCallGMRESPrecond(RefGmresFn fn, BfMat const *A, BfMat const *M, const double *b, int64_t n, double tol, int64_t maxNumIter, double *x, int64_t *numIter) {
   BfMatDenseComplex *B = bfMatDenseComplexNewViewFromPtr((BfSize)n, 1, (BfComplex *)b);
   BfSize it = 0;
   double t0 = refNow();
-  BfMat *X = fn(A, bfMatDenseComplexToMat(B), NULL, tol, (BfSize)maxNumIter, &it, NULL);
+  BfMat *X = fn(A, bfMatDenseComplexToMat(B), NULL, tol, (BfSize)maxNumIter, &it, M);
   double t1 = refNow();
   *numIter = X ? (int64_t)it : -1;
   if (X) {

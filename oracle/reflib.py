@@ -157,6 +157,26 @@ class Helm2:
         t = self.drv.refSolveGMRES(self.mat, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
         return x, it.value, t
 
+    def make_block_jacobi(self, num_blocks: int = 8, weight: float | None = None):
+        """The block Jacobi left preconditioner of multiple_scattering_context.c:544-600 for the
+        second-kind operator: a MatBlockDiag of LU views (bfMatSolve = LU solves).  Returns a BfMat*."""
+        self.drv.refHelm2MakeBlockJacobi.argtypes = [C.c_void_p, C.c_int64, C.c_double]
+        self.drv.refHelm2MakeBlockJacobi.restype = C.c_void_p
+        return self.drv.refHelm2MakeBlockJacobi(self.h, int(num_blocks), float(2 * np.pi / self.n if weight is None else weight))
+
+    def solve_gmres_precond(self, b: np.ndarray, M, tol: float = 1e-12, max_iter: int = 50, cuda: bool = False):
+        """bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, M) — or bfCudaSolveGMRESMat with the same
+        arguments when `cuda` (operator attached).  Returns (x, num_iter, seconds)."""
+        d = self.drv
+        d.refCallGMRESPrecond.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int64, C.c_void_p, C.POINTER(C.c_int64)]
+        d.refCallGMRESPrecond.restype = C.c_double
+        fn = C.cast(load_attach().bfCudaSolveGMRESMat if cuda else _ref.bfSolveGMRES, C.c_void_p)
+        b = np.ascontiguousarray(b, dtype=np.complex128).reshape(-1)
+        x = np.zeros_like(b)
+        it = C.c_int64()
+        t = d.refCallGMRESPrecond(fn, self.mat, M, b.ctypes.data, len(b), float(tol), int(max_iter), x.ctypes.data, C.byref(it))
+        return x, it.value, t
+
     def solve_gmres_cuda(self, b: np.ndarray, tol: float = 1e-12, max_iter: int = 50):
         """bfCudaSolveGMRESMat (include/bf_cuda_attach.h): the bfSolveGMRES-shaped entry point of the
         attach layer, called with reference objects.  The operator must be attached."""

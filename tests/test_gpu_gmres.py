@@ -42,6 +42,32 @@ def test_device_gmres_matches_bfSolveGMRES(n, k, tol, max_iter):
         h.close()
 
 
+@needs_ref
+@pytest.mark.parametrize("tol,max_iter", [(1e-12, 50), (1e-6, 50), (1e-12, 3)])
+def test_left_preconditioned_gmres_matches_bfSolveGMRES(tol, max_iter):
+    """bfSolveGMRES(A, B, NULL, tol, maxNumIter, &numIter, M) with the block Jacobi LU preconditioner of
+    multiple_scattering_context.c:544-600,803-810, against bfCudaSolveGMRESMat with the same arguments:
+    the operator applies run on the GPU, bfMatSolve(M, .) on the host as in the reference."""
+    n = 2048
+    h = reflib.Helm2(reflib.circle_points(n), 50.0)
+    try:
+        h.make_second_kind()
+        M = h.make_block_jacobi(8)
+        b = reflib.randn_complex(n, 0)
+        x_ref, it_ref, _ = h.solve_gmres_precond(b, M, tol, max_iter)
+        h.attach()
+        x_att, it_att, _ = h.solve_gmres_precond(b, M, tol, max_iter)             # reference GMRES, GPU applies
+        x_dev, it_dev, _ = h.solve_gmres_precond(b, M, tol, max_iter, cuda=True)  # Arnoldi on the device
+        h.detach()
+        assert it_att == it_ref and it_dev == it_ref, (it_ref, it_att, it_dev)
+        assert np.linalg.norm(x_att - x_ref) / np.linalg.norm(x_ref) <= X_TOL
+        assert np.linalg.norm(x_dev - x_ref) / np.linalg.norm(x_ref) <= X_TOL
+        x_plain, _, _ = h.solve_gmres(b, tol, max_iter)
+        assert not np.array_equal(x_plain, x_ref)   # the preconditioner changed the iteration
+    finally:
+        h.close()
+
+
 def test_device_gmres_on_synthetic_operator_with_initial_iterate():
     """No reference needed: A = 0.5 I + (small HODBF), x0 != 0; the result must solve the system as
     checked with the oracle apply, and a zero right-hand side returns zero at iteration 0."""
