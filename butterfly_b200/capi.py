@@ -173,6 +173,8 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
+    "bfCudaPlanBuildHelm2",
+    "bfCudaHelm2Evaluate",
     "bfCudaRawOpsSave",
     "bfCudaRawOpsLoad",
     "bfCudaRawOpsFree",
@@ -190,6 +192,16 @@ ATTACH_EXPORTED_SYMBOLS = [
     "bfCudaMatGetPlan",
     "bfCudaMatSetPerms",
     "bfCudaSolveGMRESMat",
+    "bfCudaMatAttachHelm2",
+]
+# libbfcuda_helm2.so (csrc/bf_helm2_record.c): the recorder of the reference's Helmholtz value builders
+HELM2_EXPORTED_SYMBOLS = [
+    "bfCudaHelm2RecordBegin",
+    "bfCudaHelm2RecordEnd",
+    "bfCudaHelm2RecordingFree",
+    "bfCudaHelm2Resolve",
+    "bfHelm2GetKernelMatrix",
+    "bfHelm2GetReexpansionMatrix",
 ]
 
 _lib = None

@@ -182,19 +182,34 @@ static int isAttached(BfMat const *A) {
   return A && A->vtbl && A->vtbl->Mul == attachedMul && wrapperOf(A)->magic == WRAPPER_MAGIC;
 }
 
-BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) {
+/* bf_helm2_record.c (libbfcuda_helm2.so); absent unless that library is loaded */
+extern BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *, BfCudaPlanDesc *, BfCudaHelm2Build *) __attribute__((weak));
+
+static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHelm2Recording *rec,
+                               BfCudaHelm2Stats *stats) {
   if (!A) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   if (isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  if (rec && !bfCudaHelm2Resolve) return BF_CUDA_ERROR_NOT_IMPLEMENTED;
   BfCudaPlanDesc *desc = NULL;
   BfCudaStatus st = bfCudaFlattenEx(A, opts ? opts->flattenFlags : 0u, &desc);
   if (st != BF_CUDA_OK) return st;
   desc->device = opts ? opts->device : -1;
   desc->buildTranspose = opts ? opts->buildTranspose : 0;
+  BfCudaHelm2Build build;
+  /* recorded leaves: map them to their recipes and strip the (inaccessible) value pointers */
+  if (rec) st = bfCudaHelm2Resolve(rec, desc, &build);
   BfCudaPlan *plan = NULL;
-  st = bfCudaPlanCreate(desc, &plan);
+  if (st == BF_CUDA_OK) st = bfCudaPlanCreate(desc, &plan);
   int dtype = desc->dtype;
   bfCudaFlattenFree(desc);
   if (st != BF_CUDA_OK) return st;
+  if (rec) {
+    st = bfCudaPlanBuildHelm2(plan, &build, stats);
+    if (st != BF_CUDA_OK) {
+      bfCudaPlanDestroy(plan);
+      return st;
+    }
+  }
   Wrapper *w = calloc(1, sizeof *w);
   if (!w) {
     bfCudaPlanDestroy(plan);
@@ -215,6 +230,14 @@ BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) {
   if (w->orig->Delete) w->vt.Delete = attachedDelete;
   A->vtbl = &w->vt;
   return BF_CUDA_OK;
+}
+
+BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) { return attachWith(A, opts, NULL, NULL); }
+
+BfCudaStatus bfCudaMatAttachHelm2(BfMat *A, BfCudaHelm2Recording *rec, BfCudaAttachOpts const *opts,
+                                  BfCudaHelm2Stats *stats) {
+  if (!rec) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  return attachWith(A, opts, rec, stats);
 }
 
 BfCudaStatus bfCudaMatDetach(BfMat *A) {

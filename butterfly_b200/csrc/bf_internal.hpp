@@ -1,0 +1,80 @@
+// bf_internal.hpp — definitions shared by the translation units that implement the C ABI
+// (bf_capi.cu: plan life cycle and apply; bf_helm2.cu: on-device construction of factor values).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "bf_cuda.h"
+#include "bf_kernels.cuh"
+#include "bf_plan.hpp"
+
+namespace bfc {
+// Records the thread-local message behind bfCudaLastErrorMessage and returns `st`.
+BfCudaStatus fail(BfCudaStatus st, const std::string &msg);
+} // namespace bfc
+
+#define BF_CUDA_TRY(expr)                                                                     \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      BfCudaStatus st_ = e_ == cudaErrorMemoryAllocation ? BF_CUDA_ERROR_OUT_OF_MEMORY       \
+                                                          : BF_CUDA_ERROR_RUNTIME;            \
+      return bfc::fail(st_, std::string(#expr) + ": " + cudaGetErrorString(e_));             \
+    }                                                                                         \
+  } while (0)
+
+namespace bfc {
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) return;
+    ok = prev == dev || cudaSetDevice(dev) == cudaSuccess;
+    if (prev == dev) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct DevDirection {
+  bool built = false;
+  Direction host;
+  // all stages concatenated; per-stage element offsets below
+  DevItem *items = nullptr;
+  DevTile *tiles = nullptr;
+  uint32_t *qItemBegin = nullptr, *qTileBegin = nullptr;
+  uint64_t *qPool16 = nullptr;
+  unsigned char *pool = nullptr;
+  std::vector<size_t> itemOff, tileOff; // per stage
+  int64_t tableBytes = 0;
+  void release() {
+    cudaFree(items); cudaFree(tiles); cudaFree(qItemBegin); cudaFree(qTileBegin); cudaFree(qPool16); cudaFree(pool);
+    items = nullptr; tiles = nullptr; qItemBegin = qTileBegin = nullptr; qPool16 = nullptr; pool = nullptr;
+    built = false;
+  }
+};
+} // namespace bfc
+
+struct BfCudaPlan {
+  int device = 0;
+  int numSMs = 148;
+  int dtype = BF_CUDA_REAL_F64;
+  int64_t numRows = 0, numCols = 0, numOps = 0;
+  bfc::DevDirection dir[3];
+  cudaStream_t stream = nullptr;
+  // scratch: [workspace | staged X], (re)grown on demand
+  unsigned char *scratch = nullptr;
+  size_t scratchBytes = 0;
+  // host-API I/O buffers
+  unsigned char *ioX = nullptr, *ioY = nullptr;
+  size_t ioXBytes = 0, ioYBytes = 0;
+  // fused caller-side permutations (scatter form) and their inverses
+  int32_t *inPerm = nullptr, *outPerm = nullptr, *invInPerm = nullptr, *invOutPerm = nullptr;
+  int64_t lastLaunches = 0;
+  bool profiling = false;
+  std::vector<cudaEvent_t> events;
+  int64_t lastStages = 0;
+  size_t maxScratchBytes = size_t(24) << 30;
+};
+

@@ -261,6 +261,60 @@ BfCudaStatus bfCudaRawOpsSave(const BfCudaPlanDesc *desc, const char *path);
 BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **desc);
 void bfCudaRawOpsFree(BfCudaPlanDesc *desc);
 
+/* ---- on-device construction of Helmholtz factor values ----------------------
+ * The reference computes every leaf of a fac_helm2 operator with one of two builders:
+ *   bfHelm2GetKernelMatrix       (src/helm2.c:282-319)  Z[i][j] = G(tgt_i, src_j)
+ *   bfHelm2GetReexpansionMatrix  (src/helm2.c:321-365)  Z_equiv \ Z_orig, a truncated-SVD least
+ *                                                       squares (src/mat_dense_complex.c:1768-1850)
+ * A "recipe" is the argument list of one such call.  bfCudaPlanBuildHelm2 evaluates the recipes on
+ * the GPU and writes the values straight into the plan's packed pool (every built direction), so the
+ * O(N^1.4) value computation and the host->device upload of the factors both disappear.  The plan must
+ * have been created from raw ops with val == NULL for the leaves named in opRecipe.
+ *
+ * Points and unit normals live in ONE pool of (x, y) pairs; recipes index it in pairs. */
+typedef enum BfCudaHelm2Kind { BF_CUDA_HELM2_KERNEL = 0, BF_CUDA_HELM2_REEXPANSION = 1 } BfCudaHelm2Kind;
+
+/* Values of the reference's BfLayerPotential (include/bf/layer_pot.h:29-43). */
+enum { BF_CUDA_LAYER_POT_SINGLE = 1, BF_CUDA_LAYER_POT_PV_DOUBLE = 2,
+       BF_CUDA_LAYER_POT_PV_NORMAL_DERIV_SINGLE = 3, BF_CUDA_LAYER_POT_COMBINED_FIELD = 5 };
+
+typedef struct BfCudaHelm2Recipe {
+  int32_t kind;       /* BfCudaHelm2Kind */
+  int32_t layerPot;   /* BF_CUDA_LAYER_POT_* (BfHelm2::layerPot, include/bf/helm2.h:10-15) */
+  double k;           /* wavenumber */
+  double alpha[2], beta[2]; /* combined field: alpha S + beta D (re, im) */
+  int64_t rows, cols; /* shape of the result: KERNEL numTgt x numSrc, REEXPANSION numEquiv x numSrc */
+  int64_t src, numSrc;     /* (original) source points: first pair, count */
+  int64_t tgt, numTgt;     /* target points */
+  int64_t equiv, numEquiv; /* REEXPANSION: equivalent sources */
+  int64_t srcNormals, tgtNormals, equivNormals; /* first pair of the unit normals, -1 = none */
+} BfCudaHelm2Recipe;
+
+typedef struct BfCudaHelm2Build {
+  int64_t numPairs;
+  const double *pairs;               /* [2 * numPairs] */
+  int64_t numRecipes;
+  const BfCudaHelm2Recipe *recipes;
+  int64_t numOps;                    /* == raw ops of the plan */
+  const int64_t *opRecipe;           /* [numOps] recipe whose result raw op i stores (whole matrix,
+                                        ld == cols), or -1: leave the leaf's pool values alone */
+} BfCudaHelm2Build;
+
+typedef struct BfCudaHelm2Stats {
+  int64_t kernelRecipes, kernelEntries;   /* leaves evaluated directly into the pool */
+  int64_t reexpRecipes, reexpEntries;     /* least-squares leaves */
+  int64_t reexpSmall, reexpLarge;         /* solved in shared memory / in global scratch */
+  int64_t maxSweeps;                      /* most Jacobi sweeps any problem needed */
+  int64_t notConverged;                   /* problems that hit the sweep limit */
+  double kernelMs, reexpMs, packMs;       /* device time per phase */
+} BfCudaHelm2Stats;
+
+BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *plan, const BfCudaHelm2Build *build, BfCudaHelm2Stats *stats);
+
+/* The two builders on their own (tests, and callers that want the matrix rather than a plan): the result
+ * of recipe `index`, row-major rows x cols complex doubles, to host memory. */
+BfCudaStatus bfCudaHelm2Evaluate(const BfCudaHelm2Build *build, int64_t index, void *out, int32_t device);
+
 /* ---- misc ---------------------------------------------------------------------------------- */
 /* Measured fp64 ceilings of `device` (-1 = current) in TFLOP/s: a register-resident DFMA loop and a
  * DMMA (mma.sync.m8n8k4.f64) loop, ~20 ms each.  The roofline denominators of the many-RHS apply

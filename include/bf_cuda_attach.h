@@ -60,6 +60,33 @@ BfCudaPlan *bfCudaMatGetPlan(BfMat const *A);
  * examples/simple/helm2_bie.c:70-81,139) into an attached object's plan. */
 BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *outPerm);
 
+/* ---- GPU construction of a fac_helm2 operator's values -------------------------
+ * libbfcuda_helm2.so (bf_helm2_record.c) defines the reference's two value builders,
+ * bfHelm2GetKernelMatrix and bfHelm2GetReexpansionMatrix (src/helm2.c:282-365), and must come before
+ * libbutterfly in the global symbol scope.  Outside a recording they forward to the reference.  Inside
+ * one they only note their arguments and return value-less leaves, so the reference's own
+ * bfFacHelm2Make / bfFacHelm2MakeMultilevel (src/fac_helm2.c:653-1002) lays out the operator without
+ * computing a single Hankel function or SVD:
+ *
+ *     bfCudaHelm2RecordBegin();
+ *     BfMat *A = bfFacHelm2MakeMultilevel(&helm, tree, tree);   // structure only
+ *     bfCudaHelm2RecordEnd(&rec);
+ *     bfCudaMatAttachHelm2(A, rec, NULL, NULL);                 // values computed on the GPU
+ *     bfCudaHelm2RecordingFree(rec);
+ *     Y = bfMatMul(A, X);                                       // as before
+ *
+ * The leaves of `A` hold no host values: after bfCudaMatDetach the object can only be deleted. */
+typedef struct BfCudaHelm2Recording BfCudaHelm2Recording;
+BfCudaStatus bfCudaHelm2RecordBegin(void);
+BfCudaStatus bfCudaHelm2RecordEnd(BfCudaHelm2Recording **rec);
+void bfCudaHelm2RecordingFree(BfCudaHelm2Recording *rec);
+/* Map the leaves of a flattened operator (bfCudaFlatten) to the recipes recorded for them: fills
+ * `build` (pointers borrowed from `rec`) and sets val = NULL on those leaves. */
+BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *rec, BfCudaPlanDesc *desc, BfCudaHelm2Build *build);
+/* bfCudaMatAttach for an operator laid out inside a recording. */
+BfCudaStatus bfCudaMatAttachHelm2(BfMat *A, BfCudaHelm2Recording *rec, BfCudaAttachOpts const *opts,
+                                  BfCudaHelm2Stats *stats);
+
 /* Drop-in for bfSolveGMRES (src/linalg.c:47-49, same signature and ownership) on an attached
  * operator: the Arnoldi process runs on the GPU (bfCudaSolveGMRES) instead of round-tripping every
  * Krylov vector through bfMatMul.  One complex right-hand side.  A non-NULL M (left preconditioner) is

@@ -28,9 +28,17 @@ def test_attach_library_exports(lib):
 
     if not capi.ATTACH_LIB_PATH.exists():
         pytest.skip("attach layer is only built where the reference headers exist")
-    out = __import__("subprocess").run(["nm", "-D", "--defined-only", str(capi.ATTACH_LIB_PATH)], capture_output=True, text=True).stdout
+    nm = lambda p: __import__("subprocess").run(["nm", "-D", "--defined-only", str(p)], capture_output=True, text=True).stdout
+    out = nm(capi.ATTACH_LIB_PATH)
+    helm2 = nm(capi.LIB_DIR / "libbfcuda_helm2.so")
     for n in _declared("bf_cuda_attach.h"):
+        # the recorder half of the header lives in libbfcuda_helm2.so (it must precede libbutterfly)
+        where = helm2 if n in capi.HELM2_EXPORTED_SYMBOLS else out
+        assert f" T {n}" in where, n
+    for n in capi.ATTACH_EXPORTED_SYMBOLS:
         assert f" T {n}" in out, n
+    for n in capi.HELM2_EXPORTED_SYMBOLS:
+        assert f" T {n}" in helm2, n
 
 
 def test_no_device_fails_loudly(lib):

@@ -1,0 +1,78 @@
+"""The reference-facing flow of the on-device construction, end to end, in one process:
+
+    bfCudaHelm2RecordBegin(); A = bfFacHelm2MakeMultilevel(...); bfCudaHelm2RecordEnd(&rec);
+    bfCudaMatAttachHelm2(A, rec, ...);  Y = bfMatMul(A, X)
+
+next to the unmodified reference building the same operator with its own value builders (the recorder
+forwards to them outside a recording) and to the dense kernel matrix, which is what the reference's own
+check compares against (examples/simple/bf_all_blocks.c:149-153).  Prints one JSON line.  A separate
+process because libbfcuda_helm2.so has to enter the symbol scope before the reference library.
+
+usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference]
+"""
+import ctypes as C
+import json
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def main():
+    n, k = int(sys.argv[1]), float(sys.argv[2])
+    import numpy as np
+
+    from butterfly_b200 import capi, helm2
+
+    rec_lib = C.CDLL(str(helm2.HELM2_LIB_PATH), mode=C.RTLD_GLOBAL)
+    from oracle import reflib
+
+    att = reflib.load_attach()
+    rec_lib.bfCudaHelm2RecordEnd.argtypes = [C.POINTER(C.c_void_p)]
+    rec_lib.bfCudaHelm2RecordingFree.argtypes = [C.c_void_p]
+    att.bfCudaMatAttachHelm2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(helm2.Stats)]
+    att.bfCudaMatAttachHelm2.restype = C.c_int32
+    pts = reflib.circle_points(n)
+    x = reflib.randn_complex(n, 0)
+    X = np.stack([x, np.conj(x), 1j * np.roll(x, 3)], axis=1)
+    out = {"n": n, "k": k}
+
+    t0 = time.time()
+    assert rec_lib.bfCudaHelm2RecordBegin() == 0
+    h = reflib.Helm2(pts, k)                      # the reference's own layout code, no values
+    handle = C.c_void_p()
+    assert rec_lib.bfCudaHelm2RecordEnd(C.byref(handle)) == 0
+    out["layout_s"] = time.time() - t0
+    st = helm2.Stats()
+    t1 = time.time()
+    code = att.bfCudaMatAttachHelm2(h.mat, handle, None, C.byref(st))
+    if code != 0:
+        raise SystemExit(f"bfCudaMatAttachHelm2: status {code}: {capi.load_library().bfCudaLastErrorMessage().decode()}")
+    out["attach_s"] = time.time() - t1
+    out["gpu_build_s"] = time.time() - t0
+    out["stats"] = st.as_dict()
+    rec_lib.bfCudaHelm2RecordingFree(handle)
+    y_gpu, _ = h.matmul(x)                        # bfMatMul through the swapped vtable
+    Y_gpu, _ = h.matmul(X)
+    out["multi_rhs_consistent"] = float(np.linalg.norm(Y_gpu[:, 0] - y_gpu[:, 0]) / np.linalg.norm(y_gpu))
+
+    if "--no-reference" not in sys.argv:
+        t2 = time.time()
+        h_ref = reflib.Helm2(pts, k)              # not recording: the reference computes its own values
+        out["reference_build_s"] = time.time() - t2
+        y_ref, _ = h_ref.matmul(x)
+        out["rel_l2_vs_reference"] = float(np.linalg.norm(y_gpu - y_ref) / np.linalg.norm(y_ref))
+        if "--no-dense" not in sys.argv:
+            Kx = h_ref.dense_kernel() @ x
+            out["reference_vs_dense"] = float(np.linalg.norm(y_ref[:, 0] - Kx) / np.linalg.norm(Kx))
+            out["gpu_built_vs_dense"] = float(np.linalg.norm(y_gpu[:, 0] - Kx) / np.linalg.norm(Kx))
+    print(json.dumps(out))
+    sys.stdout.flush()
+    import os
+    os._exit(0)
+
+
+if __name__ == "__main__":
+    main()
