@@ -465,6 +465,22 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:
             lbo = {"error": str(e)[:200]}
 
+    gpu_build = None
+    if not args.no_extra and nrhs == 1 and world == 1:
+        # side measurement, SURVEY §8f-4: the operator's VALUES computed on the GPU (bfCudaMatAttachHelm2) next to
+        # the unmodified reference building the same operator on the host, both checked against sampled rows of
+        # the dense kernel matrix (the reference's own yardstick, bf_all_blocks.c:149-153)
+        try:
+            nb = int(os.environ.get("BF_BENCH_BUILD_N", 65536))
+            r = subprocess.run([sys.executable, str(ROOT / "tools" / "helm2_gpu_build_check.py"), str(nb), repr(nb / 40.96),
+                                "--no-dense", "--sample-rows", "256"], capture_output=True, text=True, timeout=600)
+            gpu_build = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": (r.stdout + r.stderr)[-300:]}
+            if "reference_build_s" in gpu_build:
+                gpu_build["speedup_vs_reference_build"] = gpu_build["reference_build_s"] / gpu_build["gpu_build_s"]
+                gpu_build["workload"] = f"helm2_circle N={nb} k={nb / 40.96:g}: layout by the reference's fac_helm2 inside a recording, values by bfHelm2Pinv / bfHelm2Fill"
+        except Exception as e:
+            gpu_build = {"error": str(e)[:200]}
+
     rows_extra = None
     if not args.no_extra and nrhs == 1 and world > 1:
         # side measurement, configs[4]: the SAME operator block-row sharded over the ranks (strong scaling)
@@ -501,6 +517,7 @@ def run_ours(args, rank, local_rank, world):
             "cpu_baseline": cpu,
             "rhs256": extra,
             "lbo_real": lbo,
+            "helm2_gpu_build": gpu_build,
             "row_shard": rows_extra,
         }
         print(json.dumps(line), flush=True)

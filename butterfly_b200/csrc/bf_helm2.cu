@@ -28,6 +28,7 @@
 #include <math_constants.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -81,22 +82,30 @@ __device__ __forceinline__ void cfma(double2 &acc, double2 a, double2 b) {
   acc.y = fma(a.x, b.y, acc.y); acc.y = fma(a.y, b.x, acc.y);
 }
 
+// ---- Hankel functions (bf_hankel.inl) -----------------------------------------------------------------
+#define BF_HANKEL_FN __device__
+#define BF_HANKEL_TABLE __constant__
+#include "bf_hankel.inl"
+
 // One entry of a Helmholtz layer-potential kernel matrix (src/helm2.c:38-91 and :93-279): rows are targets,
-// columns are sources; coincident points give 0 (src/helm2.c:113).  i H0 = -Y0 + i J0.
+// columns are sources; coincident points give 0 (src/helm2.c:113).  (i / 4) (J + i Y) = (-Y + i J) / 4.
 __device__ double2 helmValue(int layerPot, double k, double2 alpha, double2 beta, double2 xs, double2 xt,
                              const double2 *ns, const double2 *nt) {
   const double r = hypot(xs.x - xt.x, xs.y - xt.y); // bfPoints2PairwiseDists, src/points.c:498
   if (r == 0) return make_double2(0.0, 0.0);
   const double kr = k * r;
   double2 S = make_double2(0.0, 0.0), D = make_double2(0.0, 0.0);
-  if (layerPot == BF_CUDA_LAYER_POT_SINGLE || layerPot == BF_CUDA_LAYER_POT_COMBINED_FIELD)
-    S = make_double2(-0.25 * y0(kr), 0.25 * j0(kr));
+  if (layerPot == BF_CUDA_LAYER_POT_SINGLE || layerPot == BF_CUDA_LAYER_POT_COMBINED_FIELD) {
+    const double2 h = hankel0(kr);
+    S = make_double2(-0.25 * h.y, 0.25 * h.x);
+  }
   if (layerPot != BF_CUDA_LAYER_POT_SINGLE) {
     // (i / 4) k H1(k r) / r * n . (x_tgt - x_src), n = source normal (D) or target normal (S')
     const double2 n = layerPot == BF_CUDA_LAYER_POT_PV_NORMAL_DERIV_SINGLE ? *nt : *ns;
     const double dot = n.x * (xt.x - xs.x) + n.y * (xt.y - xs.y);
     const double s = 0.25 * k / r * dot;
-    D = make_double2(-s * y1(kr), s * j1(kr));
+    const double2 h = hankel1(kr);
+    D = make_double2(-s * h.y, s * h.x);
   }
   if (layerPot == BF_CUDA_LAYER_POT_SINGLE) return S;
   if (layerPot == BF_CUDA_LAYER_POT_COMBINED_FIELD) {
@@ -112,7 +121,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__ order, int numProblems,
             const double2 *__restrict__ pairs, double2 *__restrict__ factors, double2 *__restrict__ work,
             int32_t *__restrict__ kkOut, int32_t *__restrict__ sweepsOut, int smemA, int smemG,
-            long long workStride) {
+            long long workStride, double cutScale, double tolScale) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   __shared__ int sRot;
   __shared__ int sKept;
@@ -146,7 +155,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
 
     // one-sided (Hestenes) Jacobi on the rows, round-robin tournament order: every round holds disjoint pairs
     const int m = (T + 1) & ~1, half = m >> 1;
-    const double tol = sqrt((double)ne) * 2.220446049250313e-16;
+    const double tol = tolScale * sqrt((double)ne) * 2.220446049250313e-16;
     int sweep = 0;
     for (; sweep < kMaxSweeps; ++sweep) {
       if (tid == 0) sRot = 0;
@@ -214,7 +223,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
       double mx = 0;
       for (int i = 0; i < T; ++i) mx = fmax(mx, s2[i]);
       const double eps = 2.220446049250313e-16;
-      const double cut = (double)(T > ne ? T : ne) * eps * sqrt(mx) + eps;
+      const double cut = cutScale * ((double)(T > ne ? T : ne) * eps * sqrt(mx) + eps);
       int kk = 0;
       const int cap = T < ne ? T : ne; // rank <= min(m, n): the reference only has that many sigma
       // keep the largest first when more than `cap` rows pass (cannot happen once the sweeps converged)
@@ -456,6 +465,13 @@ BfCudaStatus prepare(const BfCudaHelm2Build &b, const std::vector<char> &used, P
   return BF_CUDA_OK;
 }
 
+// Experiment knobs (default 1): scale of the truncation threshold / of the Jacobi convergence tolerance.
+double envScale(const char *name) {
+  const char *v = std::getenv(name);
+  const double d = v ? std::atof(v) : 1.0;
+  return d > 0 ? d : 1.0;
+}
+
 struct Uploaded {
   double2 *pairs = nullptr, *factors = nullptr;
   DevRecipe *recipes = nullptr;
@@ -495,7 +511,8 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
     double2 *work = nullptr;
     if (c.workStride) BF_CUDA_TRY(mem.alloc(&work, grid * c.workStride));
     kernel<<<(unsigned)grid, c.threads, c.smemBytes, stream>>>(u.problems, dOrder, (int)c.order.size(), u.pairs, u.factors,
-                                                                    work, u.kk, u.sweeps, c.smemA, c.smemG, (long long)c.workStride);
+                                                                    work, u.kk, u.sweeps, c.smemA, c.smemG, (long long)c.workStride,
+                                                                    envScale("BF_CUDA_HELM2_CUT_SCALE"), envScale("BF_CUDA_HELM2_TOL_SCALE"));
     BF_CUDA_TRY(cudaGetLastError());
     if (stats) { if (c.smemA && c.smemG) stats->reexpSmall += (int64_t)c.order.size(); else stats->reexpLarge += (int64_t)c.order.size(); }
   }

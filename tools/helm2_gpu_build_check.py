@@ -8,7 +8,7 @@ forwards to them outside a recording) and to the dense kernel matrix, which is w
 check compares against (examples/simple/bf_all_blocks.c:149-153).  Prints one JSON line.  A separate
 process because libbfcuda_helm2.so has to enter the symbol scope before the reference library.
 
-usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference]
+usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference] [--sample-rows R]
 """
 import ctypes as C
 import json
@@ -39,6 +39,12 @@ def main():
     X = np.stack([x, np.conj(x), 1j * np.roll(x, 3)], axis=1)
     out = {"n": n, "k": k}
 
+    # create the CUDA context outside the timed build (a fixed per-process cost, reported on its own)
+    tc = time.time()
+    a, b = C.c_double(), C.c_double()
+    capi.load_library().bfCudaMeasureFp64Peak(-1, C.byref(a), C.byref(b))
+    out["cuda_context_s"] = time.time() - tc
+
     t0 = time.time()
     assert rec_lib.bfCudaHelm2RecordBegin() == 0
     h = reflib.Helm2(pts, k)                      # the reference's own layout code, no values
@@ -58,12 +64,30 @@ def main():
     Y_gpu, _ = h.matmul(X)
     out["multi_rhs_consistent"] = float(np.linalg.norm(Y_gpu[:, 0] - y_gpu[:, 0]) / np.linalg.norm(y_gpu))
 
+    rows = want = None
+    if "--sample-rows" in sys.argv:
+        # R rows of the dense kernel matrix in tree order (scipy's Hankel function): the reference's own
+        # yardstick (bf_all_blocks.c:149-153) at sizes where the full matrix does not fit
+        from scipy.special import hankel1
+
+        R = int(sys.argv[sys.argv.index("--sample-rows") + 1])
+        tp = pts[h.perm()]
+        rows = np.random.default_rng(1).choice(n, R, replace=False)
+        d = np.hypot(tp[rows, None, 0] - tp[None, :, 0], tp[rows, None, 1] - tp[None, :, 1])
+        with np.errstate(invalid="ignore", divide="ignore"):
+            Kr = 0.25j * hankel1(0, k * d)
+        Kr[d == 0] = 0
+        want = Kr @ x
+        out["sample_rows"] = R
+        out["gpu_built_vs_dense_rows"] = float(np.linalg.norm(y_gpu[rows, 0] - want) / np.linalg.norm(want))
     if "--no-reference" not in sys.argv:
         t2 = time.time()
         h_ref = reflib.Helm2(pts, k)              # not recording: the reference computes its own values
         out["reference_build_s"] = time.time() - t2
         y_ref, _ = h_ref.matmul(x)
         out["rel_l2_vs_reference"] = float(np.linalg.norm(y_gpu - y_ref) / np.linalg.norm(y_ref))
+        if rows is not None:
+            out["reference_vs_dense_rows"] = float(np.linalg.norm(y_ref[rows, 0] - want) / np.linalg.norm(want))
         if "--no-dense" not in sys.argv:
             Kx = h_ref.dense_kernel() @ x
             out["reference_vs_dense"] = float(np.linalg.norm(y_ref[:, 0] - Kx) / np.linalg.norm(Kx))
