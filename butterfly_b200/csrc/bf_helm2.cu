@@ -68,7 +68,7 @@ struct DevProblem {
 };
 
 struct FillTile {
-  uint64_t pool16;
+  uint64_t dst;       // device address of the tile (any direction's pool)
   int32_t recipe;
   int32_t row0, col0; // origin of the piece in the direction's acting matrix
   uint16_t rows, kc;
@@ -325,7 +325,7 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
 }
 
 __global__ void __launch_bounds__(kFillThreads)
-bfHelm2Fill(unsigned char *pool, const FillTile *__restrict__ tiles, long long numTiles,
+bfHelm2Fill(const FillTile *__restrict__ tiles, long long numTiles,
             const DevRecipe *__restrict__ recipes, const DevProblem *__restrict__ problems,
             const int32_t *__restrict__ kkOf, const double2 *__restrict__ pairs,
             const double2 *__restrict__ factors, unsigned long long *counter) {
@@ -342,7 +342,7 @@ bfHelm2Fill(unsigned char *pool, const FillTile *__restrict__ tiles, long long n
     if (ti >= numTiles) break;
     const FillTile ft = tiles[ti];
     const DevRecipe rc = recipes[ft.recipe];
-    double2 *dst = reinterpret_cast<double2 *>(pool + ft.pool16 * 16ull);
+    double2 *dst = reinterpret_cast<double2 *>(ft.dst);
     const int n = (int)ft.rows * (int)ft.kc;
     if (rc.kind == BF_CUDA_HELM2_KERNEL) {
       const double2 *tg = pairs + rc.tgt, *sr = pairs + rc.src;
@@ -447,7 +447,8 @@ BfCudaStatus prepare(const BfCudaHelm2Build &b, const std::vector<char> &used, P
   // launch classes: (A and G in shared memory) by size, then (A only), then (neither)
   const size_t caps[] = {32 * 1024, 72 * 1024, 110 * 1024, smemLimit};
   out.classes.clear();
-  for (size_t c = 0; c < 4; ++c) out.classes.push_back({1, 1, c < 2 ? 256 : 512, caps[c], {}, 0});
+  const int classThreads[] = {256, 512, 1024, 1024}; // enough warps to hold a round's pairs (T / 2) at once
+  for (size_t c = 0; c < 4; ++c) out.classes.push_back({1, 1, classThreads[c], caps[c], {}, 0});
   out.classes.push_back({1, 0, 1024, smemLimit, {}, 0});
   out.classes.push_back({0, 0, 1024, 0, {}, 0});
   for (size_t i = 0; i < out.problems.size(); ++i) {
@@ -512,7 +513,8 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
     if (c.workStride) BF_CUDA_TRY(mem.alloc(&work, grid * c.workStride));
     kernel<<<(unsigned)grid, c.threads, c.smemBytes, stream>>>(u.problems, dOrder, (int)c.order.size(), u.pairs, u.factors,
                                                                     work, u.kk, u.sweeps, c.smemA, c.smemG, (long long)c.workStride,
-                                                                    envScale("BF_CUDA_HELM2_CUT_SCALE"), envScale("BF_CUDA_HELM2_TOL_SCALE"));
+                                                                    b.truncationScale > 0 ? b.truncationScale : envScale("BF_CUDA_HELM2_CUT_SCALE"),
+                                                                    envScale("BF_CUDA_HELM2_TOL_SCALE"));
     BF_CUDA_TRY(cudaGetLastError());
     if (stats) { if (c.smemA && c.smemG) stats->reexpSmall += (int64_t)c.order.size(); else stats->reexpLarge += (int64_t)c.order.size(); }
   }
@@ -533,20 +535,28 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
   return BF_CUDA_OK;
 }
 
-BfCudaStatus runFill(unsigned char *pool, const std::vector<FillTile> &tiles, const Uploaded &u, DeviceBuffers &mem,
-                     int numSMs, cudaStream_t stream) {
+BfCudaStatus runFill(const std::vector<FillTile> &tiles, const Uploaded &u, DeviceBuffers &mem, int numSMs,
+                     cudaStream_t stream, float *ms) {
   if (tiles.empty()) return BF_CUDA_OK;
   FillTile *dTiles = nullptr;
   BF_CUDA_TRY(cudaMalloc(&dTiles, tiles.size() * sizeof(FillTile)));
   cudaError_t e = cudaMemcpyAsync(dTiles, tiles.data(), tiles.size() * sizeof(FillTile), cudaMemcpyHostToDevice, stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(u.counter, 0, sizeof(unsigned long long), stream);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (e == cudaSuccess) e = cudaEventCreate(&e0);
+  if (e == cudaSuccess) e = cudaEventCreate(&e1);
   if (e == cudaSuccess) {
     const size_t grid = std::min<size_t>(tiles.size(), (size_t)numSMs * 2);
-    bfHelm2Fill<<<(unsigned)grid, kFillThreads, kFillSmemBytes, stream>>>(pool, dTiles, (long long)tiles.size(), u.recipes,
+    cudaEventRecord(e0, stream);
+    bfHelm2Fill<<<(unsigned)grid, kFillThreads, kFillSmemBytes, stream>>>(dTiles, (long long)tiles.size(), u.recipes,
                                                                          u.problems, u.kk, u.pairs, u.factors, u.counter);
     e = cudaGetLastError();
+    cudaEventRecord(e1, stream);
   }
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  if (e == cudaSuccess && ms) cudaEventElapsedTime(ms, e0, e1);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
   cudaFree(dTiles);
   (void)mem;
   if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("helm2 fill: ") + cudaGetErrorString(e));
@@ -602,38 +612,30 @@ extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Bui
   if (st != BF_CUDA_OK) return st;
 
   BF_CUDA_TRY(cudaFuncSetAttribute(bfHelm2Fill, cudaFuncAttributeMaxDynamicSharedMemorySize, kFillSmemBytes));
-  cudaEvent_t e0, e1;
-  BF_CUDA_TRY(cudaEventCreate(&e0));
-  BF_CUDA_TRY(cudaEventCreate(&e1));
-  BF_CUDA_TRY(cudaEventRecord(e0, P->stream));
+  // every tile of every stage of every built direction, in ONE launch (tiles are independent)
+  std::vector<FillTile> tiles;
   for (auto &dd : P->dir) {
     if (!dd.built) continue;
     const Direction &D = dd.host;
     for (const Stage &S : D.stages) {
-      std::vector<FillTile> tiles;
-      tiles.reserve(S.tiles.size());
       for (size_t t = 0; t < S.tiles.size(); ++t) {
         if (S.tiles[t].kc == kKcIdentity || S.tiles[t].kc == kKcDiag) continue;
         const DirOp &d = D.ops[(size_t)S.pieces[t].op];
         const int64_t r = b->opRecipe[d.rawIndex];
         if (r < 0) continue;
         FillTile f;
-        f.pool16 = S.tilePool16[t];
+        f.dst = (uint64_t)(uintptr_t)(dd.pool + S.tilePool16[t] * 16ull);
         f.recipe = (int32_t)r;
         f.row0 = S.pieces[t].row0; f.col0 = S.pieces[t].col0;
         f.rows = S.tiles[t].rows; f.kc = S.tiles[t].kc;
         f.swapRC = d.swapRC; f.conj = d.conj; f.pad = 0;
         tiles.push_back(f);
       }
-      st = runFill(dd.pool, tiles, u, mem, P->numSMs, P->stream);
-      if (st != BF_CUDA_OK) return st;
     }
   }
-  BF_CUDA_TRY(cudaEventRecord(e1, P->stream));
-  BF_CUDA_TRY(cudaEventSynchronize(e1));
   float ms = 0;
-  BF_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  st = runFill(tiles, u, mem, P->numSMs, P->stream, &ms);
+  if (st != BF_CUDA_OK) return st;
   if (stats) stats->packMs = ms;
   return BF_CUDA_OK;
 }
@@ -667,7 +669,7 @@ extern "C" BfCudaStatus bfCudaHelm2Evaluate(const BfCudaHelm2Build *b, int64_t i
     for (int64_t c0 = 0; c0 < c.cols; c0 += TC) {
       FillTile f;
       std::memset(&f, 0, sizeof f);
-      f.pool16 = pool16; f.recipe = (int32_t)index;
+      f.dst = pool16; f.recipe = (int32_t)index; // offset in elements for now, rebased below
       f.row0 = (int32_t)r0; f.col0 = (int32_t)c0;
       f.rows = (uint16_t)std::min<int64_t>(TR, c.rows - r0); f.kc = (uint16_t)std::min<int64_t>(TC, c.cols - c0);
       pool16 += (uint64_t)f.rows * f.kc;
@@ -675,15 +677,19 @@ extern "C" BfCudaStatus bfCudaHelm2Evaluate(const BfCudaHelm2Build *b, int64_t i
     }
   unsigned char *pool = nullptr;
   BF_CUDA_TRY(mem.alloc(&pool, (size_t)pool16 * 16 + 16));
+  std::vector<uint64_t> offs(tiles.size());
+  for (size_t t = 0; t < tiles.size(); ++t) { offs[t] = tiles[t].dst; tiles[t].dst = (uint64_t)(uintptr_t)(pool + offs[t] * 16ull); }
   BF_CUDA_TRY(cudaFuncSetAttribute(bfHelm2Fill, cudaFuncAttributeMaxDynamicSharedMemorySize, kFillSmemBytes));
-  st = runFill(pool, tiles, u, mem, prop.multiProcessorCount, stream);
+  st = runFill(tiles, u, mem, prop.multiProcessorCount, stream, nullptr);
   if (st != BF_CUDA_OK) return st;
   std::vector<double2> host((size_t)pool16);
   if (pool16) BF_CUDA_TRY(cudaMemcpy(host.data(), pool, (size_t)pool16 * 16, cudaMemcpyDeviceToHost));
   double2 *dst = static_cast<double2 *>(out);
-  for (const FillTile &f : tiles)
+  for (size_t t = 0; t < tiles.size(); ++t) {
+    const FillTile &f = tiles[t];
     for (int r = 0; r < f.rows; ++r)
       for (int q = 0; q < f.kc; ++q)
-        dst[(size_t)(f.row0 + r) * (size_t)c.cols + (size_t)(f.col0 + q)] = host[(size_t)f.pool16 + (size_t)r * f.kc + q];
+        dst[(size_t)(f.row0 + r) * (size_t)c.cols + (size_t)(f.col0 + q)] = host[(size_t)offs[t] + (size_t)r * f.kc + q];
+  }
   return BF_CUDA_OK;
 }

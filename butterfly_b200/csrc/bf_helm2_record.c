@@ -250,5 +250,6 @@ BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *r, BfCudaPlanDesc *desc, B
   build->recipes = r->recipes;
   build->numOps = desc->numOps;
   build->opRecipe = r->opRecipe;
+  build->truncationScale = 0.0; /* the reference's truncation rule */
   return BF_CUDA_OK;
 }

@@ -35,6 +35,7 @@ class Build(C.Structure):
         ("numPairs", C.c_int64), ("pairs", C.c_void_p),
         ("numRecipes", C.c_int64), ("recipes", C.c_void_p),
         ("numOps", C.c_int64), ("opRecipe", C.c_void_p),
+        ("truncationScale", C.c_double),
     ]
 
 
@@ -52,7 +53,8 @@ class Stats(C.Structure):
 class Recording:
     """Recipes + point pool + leaf map of one recorded operator (numpy arrays, so it can be saved)."""
 
-    def __init__(self, pairs, recipes, op_recipe):
+    def __init__(self, pairs, recipes, op_recipe, truncation_scale: float = 0.0):
+        self.truncation_scale = float(truncation_scale)  # 0: the reference's rule (BfCudaHelm2Build)
         self.pairs = np.ascontiguousarray(pairs, dtype=np.float64).reshape(-1, 2)
         self.recipes = np.ascontiguousarray(recipes, dtype=RECIPE_DTYPE)
         self.op_recipe = np.ascontiguousarray(op_recipe, dtype=np.int64)
@@ -62,6 +64,7 @@ class Recording:
         b.numPairs = len(self.pairs); b.pairs = self.pairs.ctypes.data
         b.numRecipes = len(self.recipes); b.recipes = self.recipes.ctypes.data
         b.numOps = len(self.op_recipe); b.opRecipe = self.op_recipe.ctypes.data
+        b.truncationScale = self.truncation_scale
         return b
 
     @classmethod

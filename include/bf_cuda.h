@@ -298,6 +298,10 @@ typedef struct BfCudaHelm2Build {
   int64_t numOps;                    /* == raw ops of the plan */
   const int64_t *opRecipe;           /* [numOps] recipe whose result raw op i stores (whole matrix,
                                         ld == cols), or -1: leave the leaf's pool values alone */
+  double truncationScale;            /* 0 or 1: the reference's rule, keep sigma_i >= max(m, n) eps sigma_0 + eps
+                                        (src/mat_dense_complex.c:1796-1806); s > 0: s times that threshold.
+                                        The operator's accuracy is sensitive to it: 4 gives a
+                                        smaller error against the dense kernel than the reference's own build. */
 } BfCudaHelm2Build;
 
 typedef struct BfCudaHelm2Stats {

@@ -147,6 +147,13 @@ def test_gpu_built_operator_against_reference_and_dense(recorded, reference_buil
         # deterministic: a second build writes the same bits
         helm2.build_plan(plan, rec)
         assert np.array_equal(plan.apply_host(x).reshape(-1, 1), y)
+        # BfCudaHelm2Build.truncationScale: 4x the reference's threshold drops the borderline singular
+        # directions, which is where the butterfly's error comes from — no worse than the
+        # reference-built operator against the dense matrix
+        rec4 = helm2.Recording(rec.pairs, rec.recipes, rec.op_recipe, truncation_scale=4.0)
+        helm2.build_plan(plan, rec4)
+        y4 = plan.apply_host(x).reshape(-1)
+        assert np.linalg.norm(y4 - Kx) / np.linalg.norm(Kx) <= max(1.5 * err_ref, 2e-12)
 
 
 def test_layer_potentials_with_normals():
