@@ -116,12 +116,14 @@ __device__ double2 helmValue(int layerPot, double k, double2 alpha, double2 beta
 }
 
 // ---- pseudo-inverse factors of one Z_equiv ----------------------------------------------------------
+// 64 registers per thread in every instantiation (the Jacobi loop needs ~40; only the one-off Hankel
+// evaluation of Z_equiv spills): occupancy of the small classes is what the kernel's time depends on.
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
 bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__ order, int numProblems,
             const double2 *__restrict__ pairs, double2 *__restrict__ factors, double2 *__restrict__ work,
             int32_t *__restrict__ kkOut, int32_t *__restrict__ sweepsOut, int smemA, int smemG,
-            long long workStride, double cutScale, double tolScale) {
+            long long workStride, double cutScale, double tolScale, int usePrecond) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   __shared__ int sRot;
   __shared__ int sKept;
@@ -138,8 +140,11 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
     else { A = gw; gw += (size_t)T * ne; }
     if (smemG) { G = reinterpret_cast<double2 *>(sp); sp += (size_t)T * T * sizeof(double2); }
     else G = gw;
-    double *s2 = reinterpret_cast<double *>(sp);
-    int *pos = reinterpret_cast<int *>(s2 + T);
+    double2 *vbuf = reinterpret_cast<double2 *>(sp);        // Householder vector            [T]
+    double *s2 = reinterpret_cast<double *>(vbuf + T);      // row norms^2 (singular values) [T]
+    double *cn = s2 + T;                                    // trailing column norms^2       [ne]
+    int *pos = reinterpret_cast<int *>(cn + ne);            // compaction map                [T]
+    int *cperm = pos + T;                                   // column permutation of the QR  [ne]
 
     const double2 *tg = pairs + P.tgt, *eq = pairs + P.equiv;
     const double2 *en = P.equivNormals >= 0 ? pairs + P.equivNormals : nullptr;
@@ -151,7 +156,79 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
       const int t = e / T, u = e - t * T;
       G[e] = make_double2(t == u ? 1.0 : 0.0, 0.0);
     }
+    for (int c = tid; c < ne; c += blockDim.x) cperm[c] = c;
     __syncthreads();
+
+    // Preconditioner (Drmac & Veselic): Householder QR with column pivoting, Z_equiv P = Q_h R, G <- Q_h^H.
+    // The rows of R are strongly graded, and Jacobi on them converges quadratically after ~4 sweeps instead
+    // of ~16 (cond(Z_equiv) ~ 1e15 costs plain Jacobi about one sweep per decade).  Everything is "one thread
+    // per column, loop over rows": contiguous in the row-major layout.
+    if (usePrecond) {
+      const int steps = T - 1 < ne ? T - 1 : ne;
+      for (int k = 0; k < steps; ++k) {
+        for (int c = k + tid; c < ne; c += blockDim.x) {
+          double a = 0;
+          for (int r = k; r < T; ++r) { const double2 x = A[(size_t)r * ne + c]; a = fma(x.x, x.x, fma(x.y, x.y, a)); }
+          cn[c] = a;
+        }
+        __syncthreads();
+        if (warp == 0) { // pivot = trailing column of largest norm (first one on ties)
+          double best = -1.0;
+          int bi = k;
+          for (int c = k + lane; c < ne; c += 32) if (cn[c] > best) { best = cn[c]; bi = c; }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+          }
+          if (lane == 0) { sRot = bi; s2[0] = best; }
+        }
+        __syncthreads();
+        const int piv = sRot;
+        const double nrm2 = s2[0];
+        if (nrm2 == 0.0) break; // the trailing block is exactly zero
+        if (piv != k) {
+          for (int r = tid; r < T; r += blockDim.x) {
+            const double2 t0 = A[(size_t)r * ne + k];
+            A[(size_t)r * ne + k] = A[(size_t)r * ne + piv];
+            A[(size_t)r * ne + piv] = t0;
+          }
+          if (tid == 0) { const int t0 = cperm[k]; cperm[k] = cperm[piv]; cperm[piv] = t0; }
+        }
+        __syncthreads();
+        // H = I - tau v v^H with v = x - alpha e_1, alpha = -e^{i arg x_0} ||x||:  H x = alpha e_1
+        const double2 x0 = A[(size_t)k * ne + k];
+        const double nrm = sqrt(nrm2), ax0 = sqrt(x0.x * x0.x + x0.y * x0.y);
+        const double2 ph = ax0 > 0 ? make_double2(x0.x / ax0, x0.y / ax0) : make_double2(1.0, 0.0);
+        const double tau = 1.0 / (nrm * (nrm + ax0));
+        for (int r = k + tid; r < T; r += blockDim.x) {
+          double2 v = A[(size_t)r * ne + k];
+          if (r == k) v = make_double2(ph.x * (ax0 + nrm), ph.y * (ax0 + nrm));
+          vbuf[r] = v;
+        }
+        __syncthreads();
+        // columns k+1.. of A and all columns of G:  M[k:, c] -= tau v (v^H M[k:, c])
+        for (int c = tid; c < (ne - k - 1) + T; c += blockDim.x) {
+          const bool inA = c < ne - k - 1;
+          double2 *M = inA ? A + (k + 1 + c) : G + (c - (ne - k - 1));
+          const size_t ld = inA ? (size_t)ne : (size_t)T;
+          double2 w = make_double2(0.0, 0.0);
+          for (int r = k; r < T; ++r) { const double2 v = vbuf[r]; cfma(w, make_double2(v.x, -v.y), M[(size_t)r * ld]); }
+          w.x *= tau; w.y *= tau;
+          for (int r = k; r < T; ++r) {
+            double2 y = M[(size_t)r * ld];
+            cfma(y, make_double2(-vbuf[r].x, -vbuf[r].y), w);
+            M[(size_t)r * ld] = y;
+          }
+        }
+        // column k itself becomes (alpha, 0, ..., 0)
+        for (int r = k + tid; r < T; r += blockDim.x)
+          A[(size_t)r * ne + k] = r == k ? make_double2(-ph.x * nrm, -ph.y * nrm) : make_double2(0.0, 0.0);
+        __syncthreads();
+      }
+      __syncthreads();
+    }
 
     // one-sided (Hestenes) Jacobi on the rows, round-robin tournament order: every round holds disjoint pairs
     const int m = (T + 1) & ~1, half = m >> 1;
@@ -183,14 +260,15 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
             cr += __shfl_xor_sync(0xffffffffu, cr, o);
             ci += __shfl_xor_sync(0xffffffffu, ci, o);
           }
-          const double ac = sqrt(cr * cr + ci * ci);
-          if (!(ac > tol * sqrt(a) * sqrt(b))) continue; // also skips zero rows
+          const double ac2 = cr * cr + ci * ci;
+          if (!(ac2 > tol * tol * a * b)) continue; // converged pair (also skips zero rows): no sqrt, no divide
           if (lane == 0) atomicAdd(&sRot, 1);
           // rotate [a_i; e^{i theta} a_j] by the real Jacobi angle that zeroes their inner product
-          const double2 ph = make_double2(cr / ac, ci / ac);
-          const double zeta = (b - a) / (2.0 * ac);
+          const double iac = rsqrt(ac2);
+          const double2 ph = make_double2(cr * iac, ci * iac);
+          const double zeta = 0.5 * (b - a) * iac;
           const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-          const double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
+          const double cs = rsqrt(1.0 + t * t), sn = cs * t;
           for (int c = lane; c < ne; c += 32) {
             const double2 x = ai[c], y = cmul(ph, aj[c]);
             ai[c] = make_double2(cs * x.x - sn * y.x, cs * x.y - sn * y.y);
@@ -243,7 +321,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
       if (pos[i] < 0) continue;
       const double inv = 1.0 / sqrt(s2[i]);
       const double2 x = A[e];
-      Qn[(size_t)pos[i] * ne + c] = make_double2(x.x * inv, x.y * inv);
+      Qn[(size_t)pos[i] * ne + cperm[c]] = make_double2(x.x * inv, x.y * inv); // undo the QR's column pivoting
     }
     for (int e = tid; e < T * T; e += blockDim.x) {
       const int t = e / T, i = e - t * T; // write GsT[t][pos[i]]: coalesced along i
@@ -454,7 +532,7 @@ BfCudaStatus prepare(const BfCudaHelm2Build &b, const std::vector<char> &used, P
   for (size_t i = 0; i < out.problems.size(); ++i) {
     DevProblem &p = out.problems[i];
     const size_t T = (size_t)p.T, ne = (size_t)p.ne;
-    const size_t aux = T * 12 + 64, aBytes = T * ne * 16, gBytes = T * T * 16;
+    const size_t aux = T * 28 + ne * 12 + 128, aBytes = T * ne * 16, gBytes = T * T * 16; // vbuf, s2, pos | cn, cperm
     size_t cls = 5;
     for (size_t c = 0; c < 4 && cls == 5; ++c) if (aBytes + gBytes + aux <= caps[c]) cls = c;
     if (cls == 5 && aBytes + aux <= smemLimit) cls = 4;
@@ -507,14 +585,20 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
     BF_CUDA_TRY(cudaMemcpyAsync(dOrder, c.order.data(), c.order.size() * 4, cudaMemcpyHostToDevice, stream));
     auto kernel = c.threads == 256 ? bfHelm2Pinv<256> : c.threads == 512 ? bfHelm2Pinv<512> : bfHelm2Pinv<1024>;
     BF_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smemBytes));
-    const size_t perSM = c.smemBytes ? std::max<size_t>(1, std::min<size_t>((size_t)(2048 / c.threads), (220 * 1024) / (c.smemBytes + 1024))) : 1;
-    const size_t grid = std::min<size_t>(c.order.size(), (size_t)numSMs * perSM);
+    // without this the driver may pick a small shared-memory carve-out and run ONE 32 KiB CTA per SM
+    // (the class that keeps everything in global scratch wants the L1 instead)
+    BF_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     c.smemA ? cudaSharedmemCarveoutMaxShared : cudaSharedmemCarveoutMaxL1));
+    int perSM = 1;
+    BF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kernel, c.threads, c.smemBytes));
+    const size_t grid = std::min<size_t>(c.order.size(), (size_t)numSMs * (size_t)std::max(perSM, 1));
     double2 *work = nullptr;
     if (c.workStride) BF_CUDA_TRY(mem.alloc(&work, grid * c.workStride));
     kernel<<<(unsigned)grid, c.threads, c.smemBytes, stream>>>(u.problems, dOrder, (int)c.order.size(), u.pairs, u.factors,
                                                                     work, u.kk, u.sweeps, c.smemA, c.smemG, (long long)c.workStride,
                                                                     b.truncationScale > 0 ? b.truncationScale : envScale("BF_CUDA_HELM2_CUT_SCALE"),
-                                                                    envScale("BF_CUDA_HELM2_TOL_SCALE"));
+                                                                    envScale("BF_CUDA_HELM2_TOL_SCALE"),
+                                                                    std::getenv("BF_CUDA_HELM2_NO_QR") ? 0 : 1);
     BF_CUDA_TRY(cudaGetLastError());
     if (stats) { if (c.smemA && c.smemG) stats->reexpSmall += (int64_t)c.order.size(); else stats->reexpLarge += (int64_t)c.order.size(); }
   }
@@ -612,6 +696,7 @@ extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Bui
   if (st != BF_CUDA_OK) return st;
 
   BF_CUDA_TRY(cudaFuncSetAttribute(bfHelm2Fill, cudaFuncAttributeMaxDynamicSharedMemorySize, kFillSmemBytes));
+  BF_CUDA_TRY(cudaFuncSetAttribute(bfHelm2Fill, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   // every tile of every stage of every built direction, in ONE launch (tiles are independent)
   std::vector<FillTile> tiles;
   for (auto &dd : P->dir) {
