@@ -173,12 +173,23 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
     nrhs = args.nrhs
     if world > 1 and rank != 0:
         dist.barrier()
-    raw, meta = workloads.helm2_circle(n, None)
+    rec = None
+    if args.values == "helm2" and args.shard == "rows":  # (the side block of a column-sharded run stays synthetic)
+        try:
+            raw, meta, rec = workloads.helm2_circle_recorded(n, None)
+        except Exception:
+            rec = None
+    if rec is None:
+        raw, meta = workloads.helm2_circle(n, None)
     if world > 1 and rank == 0:
         dist.barrier()
     t0 = time.time()
     fr = [float(v) for v in args.row_fractions.split(",")] if args.row_fractions else None
-    op = rowshard.RowShardedOperator(raw, world, rank, lambda loc: rowshard.GpuBackend(loc, device=local_rank, synthetic_seed=2024), fractions=fr)
+    op = rowshard.RowShardedOperator(raw, world, rank, lambda loc: rowshard.GpuBackend(loc, device=local_rank, synthetic_seed=2024, helm2_recording=rec), fractions=fr)
+    if rec is not None and not np.array_equal(op.raw.fingerprint(), raw.fingerprint()):
+        raise SystemExit("bench.py: shard() changed the op list; the recording no longer matches")
+    build_stats = op.backend.build_stats
+    del rec
     build_s = time.time() - t0
     E = int(raw.num_entries)
     g = torch.Generator(device="cuda").manual_seed(1234)  # the operand is replicated: same seed everywhere
@@ -244,6 +255,21 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
         torch.cuda.synchronize()
     barrier()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
+    # real values: the assembled result (rows gathered from their owners) against sampled dense kernel rows
+    dense_check = None
+    if build_stats is not None:
+        yfull = y.clone()
+        mask = torch.zeros(n, 1, dtype=torch.float64, device="cuda")
+        mask[r0:r1] = 1.0
+        yfull = yfull * mask
+        if world > 1:
+            dist.all_reduce(yfull, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            try:
+                dense_check = {"rows": 64, "rel_l2_vs_dense_rows": workloads.dense_rows_check(meta, yfull[:, 0].cpu().numpy(), xh[:, 0].numpy(), 64)}
+            except Exception as e:
+                dense_check = {"error": str(e)[:200]}
+        del yfull
     stats = torch.tensor([ms, e2e_s, float(op.local_entries), float(op.exchanged_rows), verify if verify is not None else -1.0], device="cuda", dtype=torch.float64)
     mx = stats.clone()
     if world > 1:
@@ -257,6 +283,8 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
            "load_imbalance_max_over_mean": float(mx[2]) / (float(stats[2]) / world), "exchanged_rows_per_apply": int(stats[3]),
            "exchange_stages": int(sum(op.stage_exchanges)), "stages": op.num_stages, "build_s": round(build_s, 1),
            "e2e_ms_per_apply": e2e_s * 1e3, "e2e_gflops": 8.0 * E * nrhs / e2e_s / 1e9,
+           "values": "real Helmholtz factors computed on the GPU, each rank its own leaves" if build_stats is not None else "synthetic",
+           "value_build": build_stats, "dense_check": dense_check,
            "gmres": solve, "y_cuts": [int(c) for c in op.y_cuts], "verify_rel_l2_vs_unsharded_max": (float(mx[4]) if args.verify else None),
            "collective": "all_to_all_single (NCCL) per exchanging stage; X replicated; Y row-owned"}
     op.backend.close()

@@ -672,7 +672,7 @@ extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Bui
   if (!any) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "plan has no built direction");
   for (const DirOp &d : any->host.ops) {
     const int64_t r = b->opRecipe[d.rawIndex];
-    if (r < 0) continue;
+    if (r < 0 || d.remote) continue; // block-row sharding: another rank builds (and applies) that leaf
     if (r >= b->numRecipes) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "opRecipe out of range");
     if (d.kind != BF_CUDA_LEAF_DENSE) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "recipe on a non-dense leaf");
     const BfCudaHelm2Recipe &c = b->recipes[r];

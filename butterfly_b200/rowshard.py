@@ -437,11 +437,21 @@ class RowShardedOperator:
 class GpuBackend:
     """Stage runner over the C ABI (bfCudaApplyStages / bfCudaPlanGetWorkspace)."""
 
-    def __init__(self, raw_local: RawOps, device: int = -1, synthetic_seed: int | None = None):
+    def __init__(self, raw_local: RawOps, device: int = -1, synthetic_seed: int | None = None, helm2_recording=None):
+        """helm2_recording: fill this rank's leaves with the real Helmholtz values (bfCudaPlanBuildHelm2 skips
+        the REMOTE ones); the recording's leaf map must be for the same op list (shard() keeps a dense-leaf
+        operator's ops as they are)."""
         from .plan import Plan
 
         self.plan = Plan(raw_local, device=device)
-        if synthetic_seed is not None:
+        self.build_stats = None
+        if helm2_recording is not None:
+            from . import helm2
+
+            if len(helm2_recording.op_recipe) != raw_local.num_ops:
+                raise ValueError("the recording does not describe this op list")
+            self.build_stats = helm2.build_plan(self.plan, helm2_recording)
+        elif synthetic_seed is not None:
             self.plan.fill_synthetic(synthetic_seed)
         self.lib = self.plan.lib
 
