@@ -677,7 +677,10 @@ extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Bui
     if (d.kind != BF_CUDA_LEAF_DENSE) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "recipe on a non-dense leaf");
     const BfCudaHelm2Recipe &c = b->recipes[r];
     const int64_t total = d.m * d.k;
-    if (d.storedCols != c.cols || total != c.rows * c.cols) return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "leaf shape differs from its recipe");
+    const int64_t rowOff = b->opRowOffset ? b->opRowOffset[d.rawIndex] : 0;
+    if (d.storedCols != c.cols || c.cols <= 0 || total % c.cols != 0 || rowOff < 0 || rowOff + total / c.cols > c.rows ||
+        (!b->opRowOffset && total != c.rows * c.cols))
+      return fail(BF_CUDA_ERROR_INCOMPATIBLE_SHAPES, "leaf shape differs from its recipe");
     if (!used[(size_t)r] && stats) {
       if (c.kind == BF_CUDA_HELM2_KERNEL) { ++stats->kernelRecipes; stats->kernelEntries += total; }
       else { ++stats->reexpRecipes; stats->reexpEntries += total; }
@@ -712,6 +715,8 @@ extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Bui
         f.dst = (uint64_t)(uintptr_t)(dd.pool + S.tilePool16[t] * 16ull);
         f.recipe = (int32_t)r;
         f.row0 = S.pieces[t].row0; f.col0 = S.pieces[t].col0;
+        // a leaf that is a row slab of its recipe: shift the STORED row (acting column when the direction swaps)
+        if (b->opRowOffset) (d.swapRC ? f.col0 : f.row0) += (int32_t)b->opRowOffset[d.rawIndex];
         f.rows = S.tiles[t].rows; f.kc = S.tiles[t].kc;
         f.swapRC = d.swapRC; f.conj = d.conj; f.pad = 0;
         tiles.push_back(f);

@@ -251,5 +251,6 @@ BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *r, BfCudaPlanDesc *desc, B
   build->numOps = desc->numOps;
   build->opRecipe = r->opRecipe;
   build->truncationScale = 0.0; /* the reference's truncation rule */
+  build->opRowOffset = NULL;    /* every leaf is a whole builder result */
   return BF_CUDA_OK;
 }

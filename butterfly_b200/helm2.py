@@ -36,6 +36,7 @@ class Build(C.Structure):
         ("numRecipes", C.c_int64), ("recipes", C.c_void_p),
         ("numOps", C.c_int64), ("opRecipe", C.c_void_p),
         ("truncationScale", C.c_double),
+        ("opRowOffset", C.c_void_p),
     ]
 
 
@@ -53,8 +54,9 @@ class Stats(C.Structure):
 class Recording:
     """Recipes + point pool + leaf map of one recorded operator (numpy arrays, so it can be saved)."""
 
-    def __init__(self, pairs, recipes, op_recipe, truncation_scale: float = 0.0):
+    def __init__(self, pairs, recipes, op_recipe, truncation_scale: float = 0.0, op_row_offset=None):
         self.truncation_scale = float(truncation_scale)  # 0: the reference's rule (BfCudaHelm2Build)
+        self.op_row_offset = None if op_row_offset is None else np.ascontiguousarray(op_row_offset, dtype=np.int64)
         self.pairs = np.ascontiguousarray(pairs, dtype=np.float64).reshape(-1, 2)
         self.recipes = np.ascontiguousarray(recipes, dtype=RECIPE_DTYPE)
         self.op_recipe = np.ascontiguousarray(op_recipe, dtype=np.int64)
@@ -65,7 +67,15 @@ class Recording:
         b.numRecipes = len(self.recipes); b.recipes = self.recipes.ctypes.data
         b.numOps = len(self.op_recipe); b.opRecipe = self.op_recipe.ctypes.data
         b.truncationScale = self.truncation_scale
+        b.opRowOffset = None if self.op_row_offset is None else self.op_row_offset.ctypes.data
         return b
+
+    def remapped(self, op_index, row_offset) -> "Recording":
+        """The same recipes for an op list derived from the recorded one: new op i is rows [row_offset[i], ...)
+        of recorded op op_index[i] (rowshard.origin_of)."""
+        op_index = np.asarray(op_index, dtype=np.int64)
+        base = self.op_row_offset[op_index] if self.op_row_offset is not None else 0
+        return Recording(self.pairs, self.recipes, self.op_recipe[op_index], self.truncation_scale, base + np.asarray(row_offset, np.int64))
 
     @classmethod
     def from_build(cls, b: Build) -> "Recording":

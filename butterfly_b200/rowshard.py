@@ -160,6 +160,22 @@ def _split_op_rows(o, bounds, dtype, has_values):
     return out
 
 
+def origin_of(raw: RawOps):
+    """(op index, acting-row offset) of every op of `raw` in the op list shard() was given (identity when
+    nothing was cut): what maps per-leaf side data — the Helmholtz recipes of helm2.Recording — through
+    the cuts."""
+    o = getattr(raw, "origin", None)
+    return o if o is not None else (np.arange(raw.num_ops, dtype=np.int64), np.zeros(raw.num_ops, np.int64))
+
+
+def _with_origin(new: RawOps, old: RawOps, src) -> RawOps:
+    src = np.asarray(src, dtype=np.int64)
+    oi, oo = origin_of(old)
+    off = new.ops["outOff"].astype(np.int64) - old.ops["outOff"].astype(np.int64)[src]
+    new.origin = (oi[src], oo[src] + off)
+    return new
+
+
 def presplit_tall_leaves(raw: RawOps, max_rows: int = 2048) -> RawOps:
     """Cut dense leaves taller than max_rows into slabs so ownership boundaries have somewhere to fall
     (e.g. the 15k-row last factors of a streamed eigenbasis).  Summation order per row is unchanged."""
@@ -167,13 +183,15 @@ def presplit_tall_leaves(raw: RawOps, max_rows: int = 2048) -> RawOps:
     tall = (ops["m"] > max_rows) & (ops["kind"] == capi.LEAF_DENSE)
     if not tall.any():
         return raw
-    out = []
+    out, src = [], []
     for i in range(raw.num_ops):
         if tall[i]:
-            out.extend(_split_op_rows(ops[i], range(max_rows, int(ops[i]["m"]), max_rows), raw.dtype, raw.values is not None))
+            parts = _split_op_rows(ops[i], range(max_rows, int(ops[i]["m"]), max_rows), raw.dtype, raw.values is not None)
         else:
-            out.append(ops[i].copy())
-    return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, np.array(out, dtype=ops.dtype), raw.values)
+            parts = [ops[i].copy()]
+        out.extend(parts)
+        src.extend([i] * len(parts))
+    return _with_origin(RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, np.array(out, dtype=ops.dtype), raw.values), raw, src)
 
 
 def split_diagonal_terms(raw: RawOps, y_cuts) -> RawOps:
@@ -183,14 +201,16 @@ def split_diagonal_terms(raw: RawOps, y_cuts) -> RawOps:
     sel = (ops["kind"] != capi.LEAF_DENSE) & (ops["outBuf"] == 1)
     if not sel.any():
         return raw
-    out = []
+    out, src = [], []
     for i in range(raw.num_ops):
         if sel[i]:
             o0 = int(ops[i]["outOff"])
-            out.extend(_split_op_rows(ops[i], [c - o0 for c in y_cuts], raw.dtype, raw.values is not None))
+            parts = _split_op_rows(ops[i], [c - o0 for c in y_cuts], raw.dtype, raw.values is not None)
         else:
-            out.append(ops[i].copy())
-    return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, np.array(out, dtype=ops.dtype), raw.values)
+            parts = [ops[i].copy()]
+        out.extend(parts)
+        src.extend([i] * len(parts))
+    return _with_origin(RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, np.array(out, dtype=ops.dtype), raw.values), raw, src)
 
 
 def choose_y_cuts(raw: RawOps, world: int, fractions=None) -> List[int]:
@@ -218,7 +238,9 @@ def mask_for_rank(raw: RawOps, owner: np.ndarray, rank: int) -> RawOps:
     ops["flags"][remote] |= LEAF_REMOTE
     if raw.values is not None:
         ops["val"][remote & (ops["kind"] == capi.LEAF_IDENTITY)] = 0
-    return RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, ops, raw.values)
+    out = RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, ops, raw.values)
+    out.origin = getattr(raw, "origin", None)
+    return out
 
 
 # ---- exchange lists -------------------------------------------------------------------------------
@@ -448,9 +470,10 @@ class GpuBackend:
         if helm2_recording is not None:
             from . import helm2
 
-            if len(helm2_recording.op_recipe) != raw_local.num_ops:
+            idx, off = origin_of(raw_local)  # leaves cut by shard() hold a row range of their recipe's matrix
+            if len(helm2_recording.op_recipe) <= int(idx.max(initial=-1)):
                 raise ValueError("the recording does not describe this op list")
-            self.build_stats = helm2.build_plan(self.plan, helm2_recording)
+            self.build_stats = helm2.build_plan(self.plan, helm2_recording.remapped(idx, off))
         elif synthetic_seed is not None:
             self.plan.fill_synthetic(synthetic_seed)
         self.lib = self.plan.lib

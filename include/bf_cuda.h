@@ -302,6 +302,9 @@ typedef struct BfCudaHelm2Build {
                                         (src/mat_dense_complex.c:1796-1806); s > 0: s times that threshold.
                                         The operator's accuracy is sensitive to it: 4 gives a
                                         smaller error against the dense kernel than the reference's own build. */
+  const int64_t *opRowOffset;        /* NULL, or [numOps]: leaf i holds the rows [opRowOffset[i], + its stored rows) of
+                                        its recipe's result and all columns (leaves cut into row slabs for block-row
+                                        sharding); NULL = every leaf is the whole matrix */
 } BfCudaHelm2Build;
 
 typedef struct BfCudaHelm2Stats {

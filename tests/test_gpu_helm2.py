@@ -217,3 +217,84 @@ def test_attach_helm2_flow_through_the_reference_api():
     assert out["multi_rhs_consistent"] <= 1e-13, out
     assert abs(out["gpu_built_vs_dense_rows"] - out["gpu_built_vs_dense"]) <= out["gpu_built_vs_dense"], out  # the row sample measures the same thing
     assert out["stats"]["notConverged"] == 0, out
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_row_sharded_build_matches_the_unsharded_one(recorded, world):
+    """Block-row sharding + on-device construction: every (emulated) rank builds only the leaves it owns —
+    bfCudaPlanBuildHelm2 skips BF_CUDA_LEAF_REMOTE ones — and the assembled result equals the unsharded
+    GPU-built operator's (same kernels, same per-element arithmetic, whatever the tiling)."""
+    import torch
+
+    from butterfly_b200 import rowshard
+
+    raw, rec = recorded
+    x = reflib.randn_complex(N, 0)
+    with Plan(raw) as plan:
+        helm2.build_plan(plan, rec)
+        y_full = plan.apply_host(x).reshape(-1)
+    shares = rowshard.RowShardedOperator.build_all_local(raw, world, lambda loc: rowshard.GpuBackend(loc, helm2_recording=rec))
+    xt = torch.from_numpy(x.reshape(-1, 1).copy()).cuda()
+    ys = [torch.full((raw.num_rows, 1), float("nan"), dtype=torch.complex128, device="cuda") for _ in range(world)]
+    rowshard.emulate_apply(shares, xt, ys)
+    torch.cuda.synchronize()
+    y = np.concatenate([yr[sh.y_range[0]:sh.y_range[1], 0].cpu().numpy() for sh, yr in zip(shares, ys)])
+    assert np.linalg.norm(y - y_full) / np.linalg.norm(y_full) <= 1e-14
+    built = [sh.backend.build_stats for sh in shares]
+    assert sum(b["kernelEntries"] + b["reexpEntries"] for b in built) == raw.num_entries  # each leaf built once
+    for sh in shares:
+        sh.backend.close()
+
+
+@pytest.mark.parametrize("num_tgt,num_equiv", [(40, 24), (24, 40), (33, 33), (1, 1), (130, 97)])
+def test_reexpansion_general_shapes_against_numpy_pinv(num_tgt, num_equiv):
+    """Z_equiv need not be square (fac_helm2 only produces square ones): over- and under-determined problems
+    against numpy's truncated pseudo-inverse with the reference's threshold, on geometry whose Z_equiv is
+    only mildly ill-conditioned so that the solutions themselves can be compared."""
+    from scipy.special import hankel1
+
+    rng = np.random.default_rng(num_tgt * 1000 + num_equiv)
+    k, num_src = 3.0, 29
+    ang = lambda n: 2 * np.pi * (np.arange(n) + 0.25) / n
+    src = 0.3 * rng.standard_normal((num_src, 2)) * 0.5
+    equiv = 0.9 * np.stack([np.cos(ang(num_equiv)), np.sin(ang(num_equiv))], axis=1)
+    tgt = 1.6 * np.stack([np.cos(ang(num_tgt)), np.sin(ang(num_tgt))], axis=1) + rng.standard_normal((num_tgt, 2)) * 0.05
+    pairs = np.concatenate([src, equiv, tgt])
+    rc = np.zeros(1, helm2.RECIPE_DTYPE)
+    rc[0] = (helm2.REEXPANSION, helm2.LAYER_POT_SINGLE, k, (0, 0), (0, 0), num_equiv, num_src, 0, num_src,
+             num_src + num_equiv, num_tgt, num_src, num_equiv, -1, -1, -1)
+    K = lambda t, s: 0.25j * hankel1(0, k * np.hypot(t[:, None, 0] - s[None, :, 0], t[:, None, 1] - s[None, :, 1]))
+    z_equiv, z_orig = K(tgt, equiv), K(tgt, src)
+    u, s, vh = np.linalg.svd(z_equiv, full_matrices=False)
+    cut = max(z_equiv.shape) * EPS * s[0] + EPS
+    keep = s >= cut
+    want = (vh[keep].conj().T / s[keep]) @ (u[:, keep].conj().T @ z_orig)
+    got = helm2.evaluate(helm2.Recording(pairs, rc, np.zeros(0, np.int64)), 0)
+    assert got.shape == want.shape == (num_equiv, num_src)
+    # directions with sigma within 100x of the cut are noise in both solvers: compare through Z_equiv as well
+    assert np.linalg.norm(z_equiv @ got - z_equiv @ want) <= 1e-11 * np.linalg.norm(z_orig)
+    if s[keep].min() > 1e-9 * s[0]:
+        assert np.linalg.norm(got - want) <= 1e-6 * np.linalg.norm(want)
+
+
+def test_leaves_cut_into_row_slabs(recorded):
+    """shard() cuts tall leaves into row slabs (rowshard.presplit_tall_leaves); such a leaf holds a row range of
+    its recipe's matrix (BfCudaHelm2Build.opRowOffset).  Forward and transposed pools against the uncut plan."""
+    from butterfly_b200 import rowshard
+
+    raw, rec = recorded
+    cut = rowshard.presplit_tall_leaves(raw, max_rows=48)
+    assert cut.num_ops > raw.num_ops
+    idx, off = rowshard.origin_of(cut)
+    assert off.max() > 0 and np.array_equal(cut.ops["m"] * cut.ops["k"] <= (raw.ops["m"] * raw.ops["k"])[idx], np.ones(cut.num_ops, bool))
+    x = reflib.randn_complex(N, 0)
+    with Plan(raw, build_transpose=1) as p0, Plan(cut, build_transpose=1) as p1:
+        helm2.build_plan(p0, rec)
+        helm2.build_plan(p1, rec.remapped(idx, off))
+        for op in (capi.OP_N, capi.OP_T):
+            y0, y1 = p0.apply_host(x, op).reshape(-1), p1.apply_host(x, op).reshape(-1)
+            assert np.linalg.norm(y1 - y0) <= 1e-14 * np.linalg.norm(y0), op
+    # a slab that runs off its recipe is refused
+    bad = rec.remapped(idx, off + 10**6)
+    with Plan(cut) as p2, pytest.raises(capi.BfCudaError):
+        helm2.build_plan(p2, bad)
