@@ -41,9 +41,9 @@ using namespace bfc;
 
 namespace {
 
-constexpr int kFillThreads = 128;
+constexpr int kFillThreads = 256;
 constexpr int kTChunk = 32;      // targets per Hankel chunk
-constexpr int kIBlock = 128;     // kept singular directions per pass (one per thread)
+constexpr int kIBlock = 128;     // kept singular directions per pass (two threads each: half the columns)
 constexpr int kMaxSweeps = 40;
 constexpr int kMaxT = 4096;      // row norms and the compaction map live in shared memory
 
@@ -349,14 +349,17 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
   const double2 *sn = rc.srcNormals >= 0 ? pairs + rc.srcNormals + C0 : nullptr;
   const double2 *Qn = factors + P.qOff, *GsT = factors + P.gOff;
   const int n = (int)ft.rows * (int)ft.kc;
-  double2 out[4];
+  constexpr int kOut = 512 / kFillThreads; // a tile holds at most 512 entries
+  constexpr int HC = NC / 2;               // columns per thread in the first product
+  const int il = tid >> 1, c0 = (tid & 1) * HC;
+  double2 out[kOut];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) out[j] = make_double2(0.0, 0.0);
+  for (int j = 0; j < kOut; ++j) out[j] = make_double2(0.0, 0.0);
   for (int i0 = 0; i0 < kk; i0 += kIBlock) {
-    const int i = i0 + tid;
-    double2 acc[NC];
+    const int i = i0 + il;
+    double2 acc[HC];
 #pragma unroll
-    for (int c = 0; c < NC; ++c) acc[c] = make_double2(0.0, 0.0);
+    for (int c = 0; c < HC; ++c) acc[c] = make_double2(0.0, 0.0);
     for (int t0 = 0; t0 < T; t0 += kTChunk) {
       __syncthreads();
       for (int e = tid; e < kTChunk * NC; e += kFillThreads) {
@@ -371,17 +374,17 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
         for (int tt = 0; tt < tEnd; ++tt) {
           const double2 g = GsT[(size_t)(t0 + tt) * T + i];
 #pragma unroll
-          for (int c = 0; c < NC; ++c) cfma(acc[c], g, Ks[tt * NC + c]);
+          for (int c = 0; c < HC; ++c) cfma(acc[c], g, Ks[tt * NC + c0 + c]);
         }
       }
     }
     __syncthreads();
 #pragma unroll
-    for (int c = 0; c < NC; ++c) Cs[tid * NC + c] = i < kk ? acc[c] : make_double2(0.0, 0.0);
+    for (int c = 0; c < HC; ++c) Cs[il * NC + c0 + c] = i < kk ? acc[c] : make_double2(0.0, 0.0);
     __syncthreads();
     const int ib = min(kIBlock, kk - i0);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < kOut; ++j) {
       const int e = tid + j * kFillThreads;
       if (e >= n) continue;
       const int ra = e / ft.kc, ca = e - ra * ft.kc;
@@ -396,13 +399,13 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
   }
   (void)nr;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int j = 0; j < kOut; ++j) {
     const int e = tid + j * kFillThreads;
     if (e < n) dst[e] = make_double2(out[j].x, ft.conj ? -out[j].y : out[j].y);
   }
 }
 
-__global__ void __launch_bounds__(kFillThreads)
+__global__ void __launch_bounds__(kFillThreads, 2)
 bfHelm2Fill(const FillTile *__restrict__ tiles, long long numTiles,
             const DevRecipe *__restrict__ recipes, const DevProblem *__restrict__ problems,
             const int32_t *__restrict__ kkOf, const double2 *__restrict__ pairs,
