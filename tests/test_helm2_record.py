@@ -109,3 +109,31 @@ def test_point_pool_is_deduplicated(recorded):
     # the proxy circles are shared by many leaves: far fewer pooled points than recipe operands
     operands = int((rec.recipes["numSrc"] + rec.recipes["numTgt"] + rec.recipes["numEquiv"]).sum())
     assert len(rec.pairs) < operands / 2
+
+
+def test_recipes_follow_the_leaves_through_sharding_cuts(recorded):
+    """rowshard cuts tall leaves into row slabs; origin_of / Recording.remapped carry every slab back to its
+    recipe and its first row inside the recipe's matrix (BfCudaHelm2Build.opRowOffset)."""
+    from butterfly_b200 import rowshard
+
+    raw, rec, _ = recorded
+    cut = rowshard.presplit_tall_leaves(raw, max_rows=40)
+    idx, off = rowshard.origin_of(cut)
+    assert cut.num_ops > raw.num_ops and len(idx) == cut.num_ops
+    o, c = raw.ops, cut.ops
+    assert np.array_equal(c["outOff"] - o["outOff"][idx], off)
+    assert np.array_equal(c["inOff"], o["inOff"][idx]) and np.array_equal(c["k"], o["k"][idx])
+    assert (off >= 0).all() and (off + c["m"] <= o["m"][idx]).all()
+    covered = np.zeros(raw.num_ops, np.int64)
+    np.add.at(covered, idx, c["m"])
+    assert np.array_equal(covered, o["m"])  # the slabs tile their leaf exactly
+    # a second round of cuts composes
+    cut2 = rowshard.presplit_tall_leaves(cut, max_rows=16)
+    idx2, off2 = rowshard.origin_of(cut2)
+    assert np.array_equal(cut2.ops["outOff"] - o["outOff"][idx2], off2)
+    masked = rowshard.mask_for_rank(cut2, np.zeros(cut2.num_ops, np.int64), 0)
+    assert np.array_equal(rowshard.origin_of(masked)[1], off2)
+    r2 = rec.remapped(idx2, off2)
+    assert np.array_equal(r2.op_recipe, rec.op_recipe[idx2]) and np.array_equal(r2.op_row_offset, off2)
+    rows = rec.recipes["rows"][r2.op_recipe]
+    assert (r2.op_row_offset + cut2.ops["m"] <= rows).all()
