@@ -581,8 +581,12 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
   BF_CUDA_TRY(cudaEventCreate(&e0));
   BF_CUDA_TRY(cudaEventCreate(&e1));
   BF_CUDA_TRY(cudaEventRecord(e0, stream));
-  for (const Prepared::Class &c : prep.classes) {
-    if (c.order.empty()) continue;
+  std::vector<cudaEvent_t> classEv(prep.classes.size() + 1, nullptr);
+  for (auto &e : classEv) BF_CUDA_TRY(cudaEventCreate(&e));
+  BF_CUDA_TRY(cudaEventRecord(classEv[0], stream));
+  for (size_t ci = 0; ci < prep.classes.size(); ++ci) {
+    const Prepared::Class &c = prep.classes[ci];
+    if (c.order.empty()) { BF_CUDA_TRY(cudaEventRecord(classEv[ci + 1], stream)); continue; }
     int32_t *dOrder = nullptr;
     BF_CUDA_TRY(mem.alloc(&dOrder, c.order.size()));
     BF_CUDA_TRY(cudaMemcpyAsync(dOrder, c.order.data(), c.order.size() * 4, cudaMemcpyHostToDevice, stream));
@@ -604,12 +608,21 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
                                                                     std::getenv("BF_CUDA_HELM2_NO_QR") ? 0 : 1);
     BF_CUDA_TRY(cudaGetLastError());
     if (stats) { if (c.smemA && c.smemG) stats->reexpSmall += (int64_t)c.order.size(); else stats->reexpLarge += (int64_t)c.order.size(); }
+    BF_CUDA_TRY(cudaEventRecord(classEv[ci + 1], stream));
   }
   BF_CUDA_TRY(cudaEventRecord(e1, stream));
   BF_CUDA_TRY(cudaEventSynchronize(e1));
   float ms = 0;
   BF_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
   cudaEventDestroy(e0); cudaEventDestroy(e1);
+  for (size_t ci = 0; ci < prep.classes.size() && ci < 6; ++ci) {
+    float cm = 0;
+    if (stats && cudaEventElapsedTime(&cm, classEv[ci], classEv[ci + 1]) == cudaSuccess) {
+      stats->pinvClassMs[ci] = cm;
+      stats->pinvClassCount[ci] = (int64_t)prep.classes[ci].order.size();
+    }
+  }
+  for (auto &e : classEv) cudaEventDestroy(e);
   if (stats) {
     stats->reexpMs = ms;
     std::vector<int32_t> sw(nP);

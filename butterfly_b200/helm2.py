@@ -45,10 +45,10 @@ class Stats(C.Structure):
 
     _fields_ = [(n, C.c_int64) for n in ("kernelRecipes", "kernelEntries", "reexpRecipes", "reexpEntries",
                                          "reexpSmall", "reexpLarge", "maxSweeps", "notConverged")] + [
-        (n, C.c_double) for n in ("kernelMs", "reexpMs", "packMs")]
+        (n, C.c_double) for n in ("kernelMs", "reexpMs", "packMs")] + [("pinvClassMs", C.c_double * 6), ("pinvClassCount", C.c_int64 * 6)]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_}
+        return {n: (list(getattr(self, n)) if n.startswith("pinvClass") else getattr(self, n)) for n, _ in self._fields_}
 
 
 class Recording:

@@ -313,7 +313,10 @@ typedef struct BfCudaHelm2Stats {
   int64_t reexpSmall, reexpLarge;         /* solved in shared memory / in global scratch */
   int64_t maxSweeps;                      /* most Jacobi sweeps any problem needed */
   int64_t notConverged;                   /* problems that hit the sweep limit */
-  double kernelMs, reexpMs, packMs;       /* device time per phase */
+  double kernelMs, reexpMs, packMs;       /* device time: (unused), bfHelm2Pinv launches, bfHelm2Fill launch */
+  double pinvClassMs[6];                  /* bfHelm2Pinv per launch class: Z_equiv and G both in shared memory
+                                             (<= 32 / 72 / 110 / 225 KiB), Z_equiv only, neither */
+  int64_t pinvClassCount[6];              /* distinct pseudo-inverses per class */
 } BfCudaHelm2Stats;
 
 BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *plan, const BfCudaHelm2Build *build, BfCudaHelm2Stats *stats);
