@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS)
 bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__ order, int numProblems,
             const double2 *__restrict__ pairs, double2 *__restrict__ factors, double2 *__restrict__ work,
             int32_t *__restrict__ kkOut, int32_t *__restrict__ sweepsOut, int smemA, int smemG,
-            long long workStride, double cutScale, double tolScale, int usePrecond) {
+            long long workStride, double cutScale, double tolScale, int usePrecond, double rankScale) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   __shared__ int sRot;
   __shared__ int sKept;
@@ -163,8 +163,19 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
     // The rows of R are strongly graded, and Jacobi on them converges quadratically after ~4 sweeps instead
     // of ~16 (cond(Z_equiv) ~ 1e15 costs plain Jacobi about one sweep per decade).  Everything is "one thread
     // per column, loop over rows": contiguous in the row-major layout.
+    // Rows of R beyond its numerical rank never reach the sweeps.  With column pivoting every column of the
+    // trailing block is bounded by the pivot's norm |r_kk|, and for these matrices the pivots fall to a plateau
+    // of pure rounding noise (~p eps |r_00|, the accumulated error of p reflections — the same size as the
+    // truncation threshold max(m, n) eps sigma_0) after ~0.4 T steps and stay there.  The factorization stops
+    // when the pivot is below rankScale (4) times that threshold: what is left is noise whose singular
+    // directions the reference's rule cuts or is indifferent to.  Measured: the operator's error
+    // against the dense kernel is unchanged in the fourth digit for rankScale 0 / 0.25 / 1 / 2 / 4, while the
+    // largest launch class (scratch in L2 / HBM) goes from 11.1 s to 7.0 s at N = 524 288.
+    int Teff = T;
     if (usePrecond) {
       const int steps = T - 1 < ne ? T - 1 : ne;
+      Teff = T < ne ? T : ne; // rows below the n_e-th are exactly zero after a full factorization
+      double first2 = 0.0;
       for (int k = 0; k < steps; ++k) {
         for (int c = k + tid; c < ne; c += blockDim.x) {
           double a = 0;
@@ -187,7 +198,10 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
         __syncthreads();
         const int piv = sRot;
         const double nrm2 = s2[0];
-        if (nrm2 == 0.0) break; // the trailing block is exactly zero
+        if (k == 0) first2 = nrm2;
+        // the trailing block is negligible (or zero, or so small that 1 / ||x||^2 would overflow)
+        const double small = rankScale * (double)(T > ne ? T : ne) * 2.220446049250313e-16;
+        if (!(nrm2 > 1e-280) || nrm2 < small * small * first2) { Teff = k; break; }
         if (piv != k) {
           for (int r = tid; r < T; r += blockDim.x) {
             const double2 t0 = A[(size_t)r * ne + k];
@@ -231,7 +245,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
     }
 
     // one-sided (Hestenes) Jacobi on the rows, round-robin tournament order: every round holds disjoint pairs
-    const int m = (T + 1) & ~1, half = m >> 1;
+    const int m = (Teff + 1) & ~1, half = m >> 1;
     const double tol = tolScale * sqrt((double)ne) * 2.220446049250313e-16;
     int sweep = 0;
     for (; sweep < kMaxSweeps; ++sweep) {
@@ -242,7 +256,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
           int i, j;
           if (q == 0) { i = m - 1; j = rd; }
           else { i = (rd + q) % (m - 1); j = (rd - q + (m - 1)) % (m - 1); }
-          if (i >= T || j >= T) continue; // the bye of an odd tournament
+          if (i >= Teff || j >= Teff) continue; // the bye of an odd tournament
           if (i > j) { const int s = i; i = j; j = s; }
           double2 *ai = A + (size_t)i * ne, *aj = A + (size_t)j * ne;
           double a = 0, b = 0, cr = 0, ci = 0; // ||a_i||^2, ||a_j||^2, sum a_i conj(a_j)
@@ -289,7 +303,7 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
     }
 
     // singular values = row norms; the reference's truncation (src/mat_dense_complex.c:1796-1806)
-    for (int i = warp; i < T; i += nWarps) {
+    for (int i = warp; i < Teff; i += nWarps) {
       double a = 0;
       for (int c = lane; c < ne; c += 32) { const double2 x = A[(size_t)i * ne + c]; a = fma(x.x, x.x, fma(x.y, x.y, a)); }
 #pragma unroll
@@ -299,14 +313,14 @@ bfHelm2Pinv(const DevProblem *__restrict__ problems, const int32_t *__restrict__
     __syncthreads();
     if (tid == 0) {
       double mx = 0;
-      for (int i = 0; i < T; ++i) mx = fmax(mx, s2[i]);
+      for (int i = 0; i < Teff; ++i) mx = fmax(mx, s2[i]);
       const double eps = 2.220446049250313e-16;
       const double cut = cutScale * ((double)(T > ne ? T : ne) * eps * sqrt(mx) + eps);
       int kk = 0;
       const int cap = T < ne ? T : ne; // rank <= min(m, n): the reference only has that many sigma
       // keep the largest first when more than `cap` rows pass (cannot happen once the sweeps converged)
       for (int i = 0; i < T; ++i) {
-        const bool keep = sqrt(s2[i]) >= cut && kk < cap;
+        const bool keep = i < Teff && sqrt(s2[i]) >= cut && kk < cap;
         pos[i] = keep ? kk++ : -1;
       }
       sKept = kk;
@@ -605,7 +619,8 @@ BfCudaStatus runPinv(const BfCudaHelm2Build &b, const Prepared &prep, DeviceBuff
                                                                     work, u.kk, u.sweeps, c.smemA, c.smemG, (long long)c.workStride,
                                                                     b.truncationScale > 0 ? b.truncationScale : envScale("BF_CUDA_HELM2_CUT_SCALE"),
                                                                     envScale("BF_CUDA_HELM2_TOL_SCALE"),
-                                                                    std::getenv("BF_CUDA_HELM2_NO_QR") ? 0 : 1);
+                                                                    std::getenv("BF_CUDA_HELM2_NO_QR") ? 0 : 1,
+                                                                    std::getenv("BF_CUDA_HELM2_RANK_SCALE") ? std::atof(std::getenv("BF_CUDA_HELM2_RANK_SCALE")) : 4.0);
     BF_CUDA_TRY(cudaGetLastError());
     if (stats) { if (c.smemA && c.smemG) stats->reexpSmall += (int64_t)c.order.size(); else stats->reexpLarge += (int64_t)c.order.size(); }
     BF_CUDA_TRY(cudaEventRecord(classEv[ci + 1], stream));
