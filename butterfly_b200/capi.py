@@ -199,6 +199,7 @@ HELM2_EXPORTED_SYMBOLS = [
     "bfCudaHelm2RecordBegin",
     "bfCudaHelm2RecordEnd",
     "bfCudaHelm2RecordingFree",
+    "bfCudaHelm2RecordingSetTruncationScale",
     "bfCudaHelm2Resolve",
     "bfHelm2GetKernelMatrix",
     "bfHelm2GetReexpansionMatrix",

@@ -45,6 +45,7 @@ struct BfCudaHelm2Recording {
   struct Slot { uint64_t hash; int64_t first, count; } *slots;
   size_t numSlots, usedSlots;
   int64_t *opRecipe;      /* filled by bfCudaHelm2Resolve */
+  double truncationScale; /* 0 = the reference's truncation rule */
   int failed;
 };
 
@@ -210,6 +211,12 @@ BfCudaStatus bfCudaHelm2RecordEnd(BfCudaHelm2Recording **rec) {
   return (*rec)->failed ? BF_CUDA_ERROR_OUT_OF_MEMORY : BF_CUDA_OK;
 }
 
+BfCudaStatus bfCudaHelm2RecordingSetTruncationScale(BfCudaHelm2Recording *r, double scale) {
+  if (!r || !(scale >= 0.0)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  r->truncationScale = scale;
+  return BF_CUDA_OK;
+}
+
 void bfCudaHelm2RecordingFree(BfCudaHelm2Recording *r) {
   if (!r) return;
   if (r == g_rec) g_rec = NULL;
@@ -250,7 +257,7 @@ BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *r, BfCudaPlanDesc *desc, B
   build->recipes = r->recipes;
   build->numOps = desc->numOps;
   build->opRecipe = r->opRecipe;
-  build->truncationScale = 0.0; /* the reference's truncation rule */
+  build->truncationScale = r->truncationScale;
   build->opRowOffset = NULL;    /* every leaf is a whole builder result */
   return BF_CUDA_OK;
 }

@@ -80,6 +80,10 @@ typedef struct BfCudaHelm2Recording BfCudaHelm2Recording;
 BfCudaStatus bfCudaHelm2RecordBegin(void);
 BfCudaStatus bfCudaHelm2RecordEnd(BfCudaHelm2Recording **rec);
 void bfCudaHelm2RecordingFree(BfCudaHelm2Recording *rec);
+/* Threshold of the truncated-SVD least squares, as a multiple of the reference's max(m, n) eps sigma_0 + eps
+ * (src/mat_dense_complex.c:1796-1806; BfCudaHelm2Build.truncationScale).  0 or 1 = the reference's rule (default);
+ * 4 gives an operator 4-13x closer to the dense kernel matrix than the reference's own build. */
+BfCudaStatus bfCudaHelm2RecordingSetTruncationScale(BfCudaHelm2Recording *rec, double scale);
 /* Map the leaves of a flattened operator (bfCudaFlatten) to the recipes recorded for them: fills
  * `build` (pointers borrowed from `rec`) and sets val = NULL on those leaves. */
 BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *rec, BfCudaPlanDesc *desc, BfCudaHelm2Build *build);

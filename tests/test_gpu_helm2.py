@@ -298,3 +298,15 @@ def test_leaves_cut_into_row_slabs(recorded):
     bad = rec.remapped(idx, off + 10**6)
     with Plan(cut) as p2, pytest.raises(capi.BfCudaError):
         helm2.build_plan(p2, bad)
+
+
+@needs_ref
+def test_truncation_scale_through_the_reference_facing_flow():
+    """bfCudaHelm2RecordingSetTruncationScale(rec, 4): the operator attached through the reference API is at
+    least as close to the dense kernel matrix as the reference-built one."""
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "helm2_gpu_build_check.py"), "4096", "100", "--truncation-scale", "4"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["truncation_scale"] == 4.0
+    assert out["gpu_built_vs_dense"] <= max(1.5 * out["reference_vs_dense"], 2e-12), out

@@ -8,7 +8,7 @@ forwards to them outside a recording) and to the dense kernel matrix, which is w
 check compares against (examples/simple/bf_all_blocks.c:149-153).  Prints one JSON line.  A separate
 process because libbfcuda_helm2.so has to enter the symbol scope before the reference library.
 
-usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference] [--sample-rows R]
+usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference] [--sample-rows R] [--truncation-scale S]
 """
 import ctypes as C
 import json
@@ -51,6 +51,10 @@ def main():
     handle = C.c_void_p()
     assert rec_lib.bfCudaHelm2RecordEnd(C.byref(handle)) == 0
     out["layout_s"] = time.time() - t0
+    if "--truncation-scale" in sys.argv:
+        rec_lib.bfCudaHelm2RecordingSetTruncationScale.argtypes = [C.c_void_p, C.c_double]
+        out["truncation_scale"] = float(sys.argv[sys.argv.index("--truncation-scale") + 1])
+        assert rec_lib.bfCudaHelm2RecordingSetTruncationScale(handle, out["truncation_scale"]) == 0
     st = helm2.Stats()
     t1 = time.time()
     code = att.bfCudaMatAttachHelm2(h.mat, handle, None, C.byref(st))
