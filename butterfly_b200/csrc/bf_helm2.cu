@@ -393,8 +393,10 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
       }
     }
     __syncthreads();
+    // row stride NC + 2 and the second half shifted by one element: the 8 lanes of a 128-bit store phase (4 rows x
+    // 2 halves) land in 8 different 16-byte bank groups (a stride of NC * 16 B put all of them in one)
 #pragma unroll
-    for (int c = 0; c < HC; ++c) Cs[il * NC + c0 + c] = i < kk ? acc[c] : make_double2(0.0, 0.0);
+    for (int c = 0; c < HC; ++c) Cs[il * (NC + 2) + (tid & 1) * (HC + 1) + c] = i < kk ? acc[c] : make_double2(0.0, 0.0);
     __syncthreads();
     const int ib = min(kIBlock, kk - i0);
 #pragma unroll
@@ -406,7 +408,7 @@ __device__ __forceinline__ void reexpTile(const FillTile &ft, const DevRecipe &r
       double2 s = out[j];
       for (int ii = 0; ii < ib; ++ii) {
         const double2 q = Qn[(size_t)(i0 + ii) * ne + R0 + rs];
-        cfma(s, make_double2(q.x, -q.y), Cs[ii * NC + cs]);
+        cfma(s, make_double2(q.x, -q.y), Cs[ii * (NC + 2) + cs + (cs >= HC ? 1 : 0)]);
       }
       out[j] = s;
     }
@@ -426,7 +428,7 @@ bfHelm2Fill(const FillTile *__restrict__ tiles, long long numTiles,
             const double2 *__restrict__ factors, unsigned long long *counter) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   double2 *Ks = reinterpret_cast<double2 *>(smemRaw);            // [kTChunk][32]
-  double2 *Cs = Ks + kTChunk * 32;                               // [kIBlock][32]
+  double2 *Cs = Ks + kTChunk * 32;                               // [kIBlock][32 + 2]
   __shared__ long long sTile;
   const int tid = threadIdx.x;
   for (;;) {
@@ -462,7 +464,7 @@ bfHelm2Fill(const FillTile *__restrict__ tiles, long long numTiles,
   }
 }
 
-constexpr int kFillSmemBytes = (kTChunk * 32 + kIBlock * 32) * (int)sizeof(double2);
+constexpr int kFillSmemBytes = (kTChunk * 32 + kIBlock * (32 + 2)) * (int)sizeof(double2);
 
 // ---- host side ---------------------------------------------------------------------------------------
 struct DeviceBuffers {

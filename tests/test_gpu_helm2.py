@@ -310,3 +310,17 @@ def test_truncation_scale_through_the_reference_facing_flow():
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["truncation_scale"] == 4.0
     assert out["gpu_built_vs_dense"] <= max(1.5 * out["reference_vs_dense"], 2e-12), out
+
+
+@needs_ref
+@pytest.mark.parametrize("geometry,n,k", [("ellipse", 4096, 60.0), ("kite", 3000, 45.0)])
+def test_other_geometries(geometry, n, k):
+    """Non-uniformly sampled closed curves (uneven quadtree leaves, unequal ranks, a point count that is not a
+    power of two): the GPU-built operator against the dense kernel matrix and the reference-built one."""
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "helm2_gpu_build_check.py"), str(n), repr(k), "--geometry", geometry],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["gpu_built_vs_dense"] <= max(3 * out["reference_vs_dense"], 5e-12), out
+    assert out["rel_l2_vs_reference"] <= max(4 * out["reference_vs_dense"], 1e-11), out
+    assert out["stats"]["notConverged"] == 0, out

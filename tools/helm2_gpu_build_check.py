@@ -9,6 +9,7 @@ check compares against (examples/simple/bf_all_blocks.c:149-153).  Prints one JS
 process because libbfcuda_helm2.so has to enter the symbol scope before the reference library.
 
 usage: python tools/helm2_gpu_build_check.py N K [--no-dense] [--no-reference] [--sample-rows R] [--truncation-scale S]
+       [--geometry circle|ellipse|kite]   (default circle; the others are non-uniformly sampled closed curves)
 """
 import ctypes as C
 import json
@@ -34,10 +35,21 @@ def main():
     rec_lib.bfCudaHelm2RecordingFree.argtypes = [C.c_void_p]
     att.bfCudaMatAttachHelm2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(helm2.Stats)]
     att.bfCudaMatAttachHelm2.restype = C.c_int32
-    pts = reflib.circle_points(n)
+    geom = sys.argv[sys.argv.index("--geometry") + 1] if "--geometry" in sys.argv else "circle"
+    if geom == "circle":
+        pts = reflib.circle_points(n)
+    else:
+        # non-uniform parameter spacing: clusters of points, uneven leaf boxes, unequal ranks
+        t = 2 * np.pi * (np.arange(n) + 0.3 * np.sin(6 * np.pi * np.arange(n) / n) * n / (6 * np.pi)) / n
+        if geom == "ellipse":
+            pts = np.stack([1.5 * np.cos(t), 0.6 * np.sin(t)], axis=1)
+        else:  # the "kite" of the boundary-integral literature
+            pts = np.stack([np.cos(t) + 0.65 * np.cos(2 * t) - 0.65, 1.5 * np.sin(t)], axis=1)
+        pts = np.ascontiguousarray(pts)
+    out_geom = geom
     x = reflib.randn_complex(n, 0)
     X = np.stack([x, np.conj(x), 1j * np.roll(x, 3)], axis=1)
-    out = {"n": n, "k": k}
+    out = {"n": n, "k": k, "geometry": out_geom}
 
     # create the CUDA context outside the timed build (a fixed per-process cost, reported on its own)
     tc = time.time()
