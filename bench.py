@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--verify", action="store_true", help="--shard rows: also apply the unsharded plan (must fit one GPU) and compare own rows")
     ap.add_argument("--values", default="helm2", choices=["helm2", "synthetic"],
                     help="helm2: the real Helmholtz factor values, computed on the GPU (bfCudaPlanBuildHelm2); synthetic: hash fill")
+    ap.add_argument("--truncation-scale", type=float, default=0.0,
+                    help="--values helm2: threshold of the truncated-SVD least squares as a multiple of the reference's rule "
+                         "(0 = the reference's rule; 4 gives a far more accurate operator, DESIGN.md 8c)")
     ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     return ap.parse_args()
@@ -354,8 +357,10 @@ def run_ours(args, rank, local_rank, world):
         from butterfly_b200 import helm2
 
         tb = time.time()
+        rec.truncation_scale = float(args.truncation_scale)
         try:
             build_stats = helm2.build_plan(plan, rec)
+            build_stats["truncation_scale"] = rec.truncation_scale
             build_stats["seconds"] = time.time() - tb
             values_note = "real Helmholtz factors computed on the GPU (bfHelm2Pinv + bfHelm2Fill)"
         except Exception as e:  # e.g. out of device memory next to the pool: measure on synthetic values and say so
