@@ -283,18 +283,31 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       cPool += bytes;
     }
 
-    // one reduction per item: over the G lanes of a row, then row r -> lane r for a coalesced store
-    T out = S::zero();
+    // One reduction per item over the G lanes of a row, then row r -> lane r for a coalesced store.  The 8
+    // passes are shared out over the lanes as the butterfly halves (lane l keeps the passes whose bit matches
+    // its own and hands the others to its partner): 4 + 2 + 1 exchanges instead of 8 x 3, and every sum is
+    // formed with the same operand pairs in the same level order as a plain xor all-reduce, i.e. bit-identical.
+    static_assert(P == 8, "the halving butterfly below shares out 8 passes");
+    if (G == 16) {
 #pragma unroll
-    for (int p = 0; p < P; ++p) {
-      if (p * RPP < rows) {
-        T v = acc[p];
-#pragma unroll
-        for (int off = G / 2; off > 0; off >>= 1) v = S::add(v, S::shflXor(v, off));
-        v = S::shfl(v, (lane % RPP) * G);
-        if (lane / RPP == p) out = v;
-      }
+      for (int p = 0; p < P; ++p) acc[p] = S::add(acc[p], S::shflXor(acc[p], 8));
     }
+    T r4[4], r2[2];
+    {
+      const bool hi = (l & 4) != 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) r4[j] = S::add(hi ? acc[j + 4] : acc[j], S::shflXor(hi ? acc[j] : acc[j + 4], 4));
+    }
+    {
+      const bool hi = (l & 2) != 0;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) r2[j] = S::add(hi ? r4[j + 2] : r4[j], S::shflXor(hi ? r4[j] : r4[j + 2], 2));
+    }
+    const bool odd = (l & 1) != 0;
+    const T mine = S::add(odd ? r2[1] : r2[0], S::shflXor(odd ? r2[0] : r2[1], 1));
+    // lane (g, l) now holds pass (l & 7) of row group g, i.e. row (l & 7) * RPP + g; row r lives in lane
+    // (r % RPP) * G + r / RPP
+    T out = S::shfl(mine, (lane % RPP) * G + lane / RPP);
     out = S::add(out, extra);
     if (lane < rows) {
       const uint32_t sp = it.outAddr >> 30;
