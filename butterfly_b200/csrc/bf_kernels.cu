@@ -98,26 +98,31 @@ __device__ __forceinline__ unsigned char *rowPtr(const StageLaunch &a, uint32_t 
 // predicates; passes are taken two at a time for ILP and left through a warp-uniform branch.
 template <bool CPLX, int NC, int P, int RPP, int G>
 __device__ __forceinline__ void tileFma(typename Scalar<CPLX>::T (&acc)[P], const typename Scalar<CPLX>::T *A,
-                                        const typename Scalar<CPLX>::T *xs, int rows, int kc, int g, int l) {
+                                        const typename Scalar<CPLX>::T *xs, const int (&rp)[P], int rows, int kc, int l) {
   using S = Scalar<CPLX>;
   using T = typename S::T;
+  // Only the LAST column chunk can run past the tile edge (NC = ceil(kc / G)): the others are addressed as
+  // base + immediate, one address register per pass instead of one per load.  rp[p] is the lane's (clamped)
+  // row of pass p, fixed for the whole item.
   T xr[NC];
-  int cj[NC];
+  const int jl = (NC - 1) * G + l;
+  const int cl = min(jl, kc - 1);
 #pragma unroll
-  for (int tt = 0; tt < NC; ++tt) {
-    const int j = tt * G + l;
-    cj[tt] = min(j, kc - 1);
-    const T v = xs[cj[tt]];
-    xr[tt] = j < kc ? v : S::zero();
+  for (int tt = 0; tt < NC - 1; ++tt) xr[tt] = xs[tt * G + l];
+  {
+    const T v = xs[cl];
+    xr[NC - 1] = jl < kc ? v : S::zero();
   }
+  const T *Al = A + l;
 #pragma unroll
   for (int p = 0; p < P; p += 2) {
     if (p * RPP >= rows) break;
-    const T *A0 = A + min(p * RPP + g, rows - 1) * kc;
-    const T *A1 = A + min((p + 1) * RPP + g, rows - 1) * kc;
+    const int o0 = rp[p] * kc, o1 = rp[p + 1] * kc;
     T a0[NC], a1[NC];
 #pragma unroll
-    for (int tt = 0; tt < NC; ++tt) { a0[tt] = A0[cj[tt]]; a1[tt] = A1[cj[tt]]; }
+    for (int tt = 0; tt < NC - 1; ++tt) { a0[tt] = Al[o0 + tt * G]; a1[tt] = Al[o1 + tt * G]; }
+    a0[NC - 1] = A[o0 + cl];
+    a1[NC - 1] = A[o1 + cl];
 #pragma unroll
     for (int tt = 0; tt < NC; ++tt) { S::fma(acc[p], a0[tt], xr[tt]); S::fma(acc[p + 1], a1[tt], xr[tt]); }
   }
@@ -242,6 +247,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
 #pragma unroll
     for (int p = 0; p < P; ++p) acc[p] = S::zero();
     T extra = S::zero();
+    int rp[P]; // this lane's row in every pass, clamped to the item's last row (edge lanes repeat it)
+#pragma unroll
+    for (int p = 0; p < P; ++p) rp[p] = min(p * RPP + g, rows - 1);
 
 #pragma unroll 1
     for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
@@ -268,14 +276,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       const T *A = reinterpret_cast<const T *>(As);
       // exact trip counts through real (warp-uniform) branches: no predicated-off FMA slots
       switch ((kc + G - 1) / G) {
-      case 1: tileFma<CPLX, 1, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 2: tileFma<CPLX, 2, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 3: tileFma<CPLX, 3, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 4: tileFma<CPLX, 4, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 5: tileFma<CPLX, 5, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 6: tileFma<CPLX, 6, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      case 7: tileFma<CPLX, 7, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
-      default: tileFma<CPLX, 8, P, RPP, G>(acc, A, xs, rows, kc, g, l); break;
+      case 1: tileFma<CPLX, 1, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 2: tileFma<CPLX, 2, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 3: tileFma<CPLX, 3, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 4: tileFma<CPLX, 4, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 5: tileFma<CPLX, 5, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 6: tileFma<CPLX, 6, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      case 7: tileFma<CPLX, 7, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
+      default: tileFma<CPLX, 8, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
       }
       __syncwarp();
       produce(); // refill the slot just drained
