@@ -287,6 +287,8 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
     a.base[kSpaceW] = P->scratch; a.ld[kSpaceW] = nc;
     a.outPerm = scatterOut;
     a.numQueues = D.numQueues; a.nrhs = (int)nc; a.colBegin = 0;
+    // overlap a stage's prologue with the previous stage's tail where stages are short (bf_kernels.cu)
+    a.pdl = (uint64_t)D.pool16 * 16ull < (4ull << 30) ? 1 : 0;
     // The 1-RHS kernel bulk-copies operand segments: they must be dense and 16-byte aligned (real
     // segments may start 8 bytes into a 16-byte window, so they always go through the padded copy).
     const bool needStage = scatterIn != nullptr || (cplx && (reinterpret_cast<uintptr_t>(xp) & 15)) || (nc == 1 && (!cplx || ldx != 1));

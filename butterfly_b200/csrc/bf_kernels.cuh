@@ -22,6 +22,7 @@ struct StageLaunch {
   int numQueues;
   int nrhs;
   int colBegin;               // first RHS column this launch handles (wide kernel)
+  int pdl;                    // 1-RHS kernel: launched with programmatic stream serialization (small operators)
 };
 
 // Shared-memory geometry of the 1-RHS kernel (one ring of kGemvSlots slots per warp).
