@@ -324,3 +324,15 @@ def test_other_geometries(geometry, n, k):
     assert out["gpu_built_vs_dense"] <= max(3 * out["reference_vs_dense"], 5e-12), out
     assert out["rel_l2_vs_reference"] <= max(4 * out["reference_vs_dense"], 1e-11), out
     assert out["stats"]["notConverged"] == 0, out
+
+
+def test_c_example_program():
+    """examples/helm2_gpu.c: the reference's bf_all_blocks program in C with the bfCuda* calls added — layout inside
+    a recording, values on the GPU, bfMatMul through the swapped vtable, 64 dense rows as the check."""
+    exe = ROOT / "examples" / "helm2_gpu"
+    if not exe.exists():
+        pytest.skip("examples/helm2_gpu is built where the reference sources exist")
+    r = subprocess.run([str(exe), "4096"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-1000:]
+    err = float(r.stdout.strip().splitlines()[-1].split(":")[1])
+    assert err <= 2e-11, r.stdout
