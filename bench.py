@@ -100,14 +100,17 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.samples)}
 
 
-def cpu_reference_leg(steps, warmup, sample_n=CPU_SAMPLE_N):
+def cpu_reference_leg(steps, warmup, sample_n=CPU_SAMPLE_N, keep=False):
     """The reference's own CPU bfMatMul (oracle/_ref = unmodified sources + OpenBLAS) on a bounded
-    sample of the workload: the same generator at a smaller N, REAL factor values, 1 RHS."""
+    sample of the workload: the same generator at a smaller N, REAL factor values, 1 RHS.  keep: also
+    return the live reference operator (for the same-factors GPU leg, configs0_block)."""
     import numpy as np
 
     from oracle import reflib
 
     if not reflib.available():
+        if keep:
+            return None, None
         # the oracle port on a synthetic operator of the same family
         from butterfly_b200 import capi, synth
         from oracle import portlib
@@ -134,13 +137,89 @@ def cpu_reference_leg(steps, warmup, sample_n=CPU_SAMPLE_N):
         t = float(np.median(ts[warmup:]))
         if best is None or t < best[0]:
             best = (t, used)
-    h.close()
+    if not keep:
+        h.close()
     t, used = best
     if E is None:
         E = int(2112 * sample_n)
-    return {"value": 8 * E / t / 1e9, "unit": "GFLOP/s", "cores": int(used), "kind": "reference",
-            "sample": f"reference bfMatMul (unmodified sources, OpenBLAS) on fac_helm2 circle N={sample_n} k={k:g} (configs[0]: same generator at the reference's own CPU size; built in {build_s:.1f}s), 1 RHS, median of {steps}, best of 1 and {ncpu} BLAS threads",
-            "ms_per_step": t * 1e3, "entries": int(E), "matvecs_per_s": 1.0 / t}
+    r = {"value": 8 * E / t / 1e9, "unit": "GFLOP/s", "cores": int(used), "kind": "reference",
+         "sample": f"reference bfMatMul (unmodified sources, OpenBLAS) on fac_helm2 circle N={sample_n} k={k:g} (configs[0]: same generator at the reference's own CPU size; built in {build_s:.1f}s), 1 RHS, median of {steps}, best of 1 and {ncpu} BLAS threads",
+         "ms_per_step": t * 1e3, "entries": int(E), "matvecs_per_s": 1.0 / t, "sample_n": sample_n}
+    return (r, h) if keep else r
+
+
+def configs0_block(local_rank):
+    """BASELINE.json configs[0] measured, not quoted: the reference builds fac_helm2 on 16 384 circle points
+    (k = 400) ONCE; the SAME object is then timed through the reference's own bfMatMul on the CPU and — after
+    bfCudaMatAttach — on the GPU (malloc'ed result, pageable operand: what a reference caller gets), plus the
+    device-resident apply of that plan against the HBM roofline, plus parity on the same factors."""
+    import numpy as np
+    import torch
+
+    from butterfly_b200 import capi
+    from butterfly_b200.plan import Plan
+    from oracle import reflib
+
+    cpu, h = cpu_reference_leg(steps=10, warmup=2, keep=True)
+    if h is None:
+        return None, None
+    out = {"workload": f"helm2_circle N={CPU_SAMPLE_N} k={CPU_SAMPLE_N / 40.96:g} nrhs=1, factors built by the reference (same object on both sides)",
+           "same_config": True, "cpu_ms_per_apply": cpu["ms_per_step"], "cpu_cores": cpu["cores"], "E": cpu["entries"]}
+    try:
+        n = CPU_SAMPLE_N
+        x = reflib.randn_complex(n, 0)
+        rng = np.random.default_rng(7)
+        X = rng.standard_normal((n, 64)) + 1j * rng.standard_normal((n, 64))
+        probe = np.arange(0, 64, 4)
+        y_cpu, _ = h.matmul(x)
+        Yp_cpu, _ = h.matmul(X[:, probe].copy())
+        t0 = time.perf_counter()
+        h.attach()
+        out["attach_s"] = time.perf_counter() - t0  # flatten + compile + upload of 554 MB of factors
+        y_gpu, _ = h.matmul(x)
+        Y_gpu, _ = h.matmul(X)
+        rel = lambda a, b: float(np.linalg.norm(a - b) / np.linalg.norm(b))
+        out["parity"] = {"rel_l2_same_factors_1rhs": rel(y_gpu, y_cpu),
+                         "rel_l2_same_factors_64rhs_max": max(rel(Y_gpu[:, c], Yp_cpu[:, i]) for i, c in enumerate(probe)),
+                         "columns_checked_of_64": len(probe), "tolerance": 1e-12}
+        if max(out["parity"]["rel_l2_same_factors_1rhs"], out["parity"]["rel_l2_same_factors_64rhs_max"]) > 1e-12:
+            raise SystemExit(f"bench.py: configs[0] parity failed: {out['parity']}")
+        ts = [h.matmul(x)[1] for _ in range(30)]
+        out["gpu_bfMatMul_ms_per_apply"] = float(np.median(ts[5:])) * 1e3  # inside bfMatMul: H2D + apply + D2H + malloc
+        out["speedup_bfMatMul_same_operator"] = out["cpu_ms_per_apply"] / out["gpu_bfMatMul_ms_per_apply"]
+        plan = Plan.borrow(h.plan_handle(), n, n)
+        stream = torch.cuda.current_stream().cuda_stream
+        xd = torch.from_numpy(x).cuda().reshape(n, 1)
+        yd = torch.empty_like(xd)
+        for _ in range(10):
+            plan.apply_device(xd, yd, stream=stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 200
+        e0.record()
+        for _ in range(reps):
+            plan.apply_device(xd, yd, stream=stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        E = plan.info["numEntries"]
+        byts = 16.0 * E + 32.0 * n
+        out.update({"device_ms_per_apply": ms, "device_gflops": 8.0 * E / (ms * 1e-3) / 1e9, "device_gbs": byts / (ms * 1e-3) / 1e9,
+                    "frac_of_hbm_peak": byts / (ms * 1e-3) / 1e9 / peaks()[0], "launches_per_apply": int(plan.last_launch_count),
+                    "l2_note": "554 MB of factors per apply: larger than L2 (126 MB), no flush needed"})
+        out["parity"]["device_vs_cpu_1rhs"] = rel(yd.cpu().numpy(), y_cpu)
+        h.detach()
+    except SystemExit:
+        raise
+    except Exception as e:
+        out["error"] = str(e)[:300]
+    finally:
+        h.close()
+    return cpu, out
+
+
+def workload_label(n, k, nrhs):
+    return f"helm2_circle N={n} k={k:g} nrhs={nrhs}/GPU"
 
 
 def run_reference(args, rank, world):
@@ -148,11 +227,15 @@ def run_reference(args, rank, world):
         return  # rank 0 alone runs the CPU arm
     r = cpu_reference_leg(args.steps, max(args.warmup, 1))
     k = args.k or args.n / 40.96
+    # `config` is our arm's (the contract: the reference arm runs on OUR config, each step a bounded sample
+    # of that workload); what was actually timed is spelled out in config.sample / cpu_baseline.sample.  The
+    # same-problem figure (same N, same factors, CPU vs GPU through bfMatMul) is our arm's `configs0` block.
     line = {
         "impl": "reference", "metric": "butterfly apply GFLOP/s (complex fp64, 1 RHS)", "value": r["value"], "unit": "GFLOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "c128 (complex f64)", "data": "synthetic",
-        "config": {"workload": f"helm2_circle N={args.n} k={k:g} nrhs=1 (timed on the bounded sample below)"},
+        "config": {"workload": workload_label(args.n, k, 1),
+                   "sample": f"timed on helm2_circle N={r.get('sample_n', CPU_SAMPLE_N)} (bounded sample: the reference needs ~11 min and 75 GB of mallocs to build N={args.n}); value is a GFLOP/s RATE"},
         "matvecs_per_s_on_sample": r.get("matvecs_per_s"),
         "cpu_baseline": {k2: r[k2] for k2 in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -169,7 +252,8 @@ def run_rows(args, rank, local_rank, world, n=None, steps=None, warmup=None):
     import torch
     import torch.distributed as dist
 
-    from butterfly_b200 import capi, rowshard, workloads
+    from butterfly_b200 import capi, rowshard
+    from tools import workloads
 
     n = n or args.n
     steps, warmup = steps or args.steps, warmup or args.warmup
@@ -304,7 +388,8 @@ def run_ours(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
 
-    from butterfly_b200 import capi, workloads
+    from butterfly_b200 import capi
+    from tools import workloads
     from butterfly_b200.plan import Plan
 
     if not torch.cuda.is_available():
@@ -491,8 +576,25 @@ def run_ours(args, rank, local_rank, world):
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 ms = float(t.item())
             tf = 8.0 * E * nr / (ms * 1e-3) / 1e12  # per GPU
+            # end to end for the block apply: bfCudaApplyHost on pinned host buffers (2 x 16 n nr bytes over PCIe)
+            e2e256 = None
+            try:
+                Xh = torch.empty(n, nr, dtype=torch.complex128).pin_memory()
+                Yh = torch.empty(n, nr, dtype=torch.complex128).pin_memory()
+                Xh.copy_(X)
+                plan.apply_host(Xh.numpy(), capi.OP_N, out=Yh.numpy())
+                t0 = time.perf_counter()
+                for _ in range(2):
+                    plan.apply_host(Xh.numpy(), capi.OP_N, out=Yh.numpy())
+                dt = (time.perf_counter() - t0) / 2
+                e2e256 = {"ms_per_apply": dt * 1e3, "gflops": 8.0 * E * nr / dt / 1e9, "h2d_bytes_per_step": int(16 * n * nr),
+                          "d2h_bytes_per_step": int(16 * n * nr), "api": "bfCudaApplyHost (pinned host buffers)",
+                          "matches_device_result": bool(torch.equal(Yh.cuda(), Y))}
+                del Xh, Yh
+            except Exception as e:
+                e2e256 = {"error": str(e)[:200]}
             extra = {"nrhs_per_gpu": nr, "ms_per_apply": ms, "gflops": tf * 1e3 * world, "matvecs_per_s": nr * world / (ms * 1e-3),
-                     "launches_per_apply": int(plan.last_launch_count),
+                     "launches_per_apply": int(plan.last_launch_count), "e2e": e2e256,
                      "clocks": clk256.summary(),
                      "roofline": {"bound": "fp64 tensor pipe (DMMA)", "kernel": "bfWideMmaStage<2>", "achieved": tf, "peak": dmma_sus.value,
                                   "unit": "TFLOP/s", "frac": tf / dmma_sus.value if dmma_sus.value else None,
@@ -542,11 +644,16 @@ def run_ours(args, rank, local_rank, world):
         try:
             nb = int(os.environ.get("BF_BENCH_BUILD_N", 65536))
             r = subprocess.run([sys.executable, str(ROOT / "tools" / "helm2_gpu_build_check.py"), str(nb), repr(nb / 40.96),
-                                "--no-dense", "--sample-rows", "256"], capture_output=True, text=True, timeout=600)
+                                "--no-dense", "--sample-rows", "256", "--same-factors"], capture_output=True, text=True, timeout=900)
             gpu_build = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": (r.stdout + r.stderr)[-300:]}
+            par = gpu_build.get("parity")
+            if par and max(par["rel_l2_same_factors_1rhs"], par["rel_l2_same_factors_256rhs_max"]) > 1e-12:
+                raise SystemExit(f"bench.py: same-factors parity failed at N={nb}: {par}")
             if "reference_build_s" in gpu_build:
                 gpu_build["speedup_vs_reference_build"] = gpu_build["reference_build_s"] / gpu_build["gpu_build_s"]
                 gpu_build["workload"] = f"helm2_circle N={nb} k={nb / 40.96:g}: layout by the reference's fac_helm2 inside a recording, values by bfHelm2Pinv / bfHelm2Fill"
+        except SystemExit:
+            raise
         except Exception as e:
             gpu_build = {"error": str(e)[:200]}
 
@@ -561,9 +668,14 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:
             rows_extra = {"error": str(e)[:300]}
 
-    cpu = None
+    cpu = configs0 = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_reference_leg(steps=10, warmup=2)
+        plan.close()  # free 67 GB before the second operator is attached
+        del x, y
+        torch.cuda.empty_cache()
+        cpu, configs0 = configs0_block(local_rank)
+        if cpu is None:
+            cpu = cpu_reference_leg(steps=10, warmup=2)
         cpu = {k2: cpu[k2] for k2 in ("value", "unit", "cores", "kind", "sample")}
 
     if rank == 0:
@@ -573,7 +685,7 @@ def run_ours(args, rank, local_rank, world):
             "value": gflops, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "c128 (complex f64)", "data": "synthetic",
-            "config": {"workload": f"helm2_circle N={n} k={k:g} nrhs={nrhs}/GPU", "structure": meta["structure"],
+            "config": {"workload": workload_label(n, k, nrhs), "structure": meta["structure"],
                        "values": values_note, "value_build": build_stats, "dense_check": dense_check,
                        "E": int(E), "pool_GB": info["poolBytes"] / 1e9, "stages": int(info["numStagesN"]),
                        "parallelism": f"rhs-columns x{world} (plan replicated, no collective)",
@@ -585,14 +697,14 @@ def run_ours(args, rank, local_rank, world):
             "gpu_launches": int(launches),
             "roofline": roof,
             "cpu_baseline": cpu,
+            "configs0": configs0,
             "rhs256": extra,
             "lbo_real": lbo,
             "helm2_gpu_build": gpu_build,
             "row_shard": rows_extra,
         }
         print(json.dumps(line), flush=True)
-    if rows_extra is None:
-        plan.close()
+    plan.close()  # idempotent
     if world > 1:
         dist.destroy_process_group()
 

@@ -10,6 +10,7 @@
  */
 #include "bf_cuda_attach.h"
 
+#include <complex.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -24,12 +25,75 @@ typedef struct Wrapper {
   BfCudaPlan *plan;
   int dtype;
   unsigned magic;
+  BfCudaAttachOpts opts; /* what the snapshot was taken with (re-used when it is refreshed) */
+  int transposed;       /* bfMatTranspose was called an odd number of times since the snapshot: the
+                           plan's reverse direction is what bfMatMul means now */
+  int dirty;            /* the host object was edited in place since the snapshot (ScaleCols,
+                           AddInplace ...): re-flatten before the next apply */
+  int valueless;        /* attached through a helm2 recording: the leaves hold no host values, so
+                           the object cannot be edited or re-flattened */
+  int64_t *inPerm, *outPerm; /* host copies of the fused permutations (survive a refresh) */
+  int64_t numInPerm, numOutPerm;
 } Wrapper;
 #define WRAPPER_MAGIC 0xBFC0DA01u
 
 static Wrapper *wrapperOf(BfMat const *A) {
   Wrapper *w = (Wrapper *)A->vtbl; /* vt is the first member */
   return w;
+}
+
+/* Run `stmt` with the object's ORIGINAL vtable in place: the reference's own implementation of a
+ * slot sees the object exactly as it was before the attach.  (Needed, not just tidy: GetView / Copy of
+ * the block types do `*view = *orig`, src/mat_product.c:31-46 — a view made while the swapped pointer
+ * is in place would carry it, and deleting that view would tear down the owner's plan.) */
+#define WITH_ORIG_VTABLE(A, w, stmt)      \
+  do {                                    \
+    BfMat *B_ = (BfMat *)(A);             \
+    BfMatVtable *mine_ = B_->vtbl;        \
+    B_->vtbl = (w)->orig;                 \
+    stmt;                                 \
+    B_->vtbl = mine_;                     \
+  } while (0)
+
+static void freeWrapper(Wrapper *w) {
+  bfCudaPlanDestroy(w->plan);
+  w->magic = 0;
+  free(w->inPerm);
+  free(w->outPerm);
+  free(w);
+}
+
+/* The plan is a snapshot of the host object.  After an in-place edit the snapshot is retaken the next
+ * time the operator is applied, so an attached object never applies stale factors. */
+static int refreshIfDirty(BfMat const *A) {
+  Wrapper *w = wrapperOf(A);
+  if (!w->dirty) return 1;
+  BfCudaPlanDesc *desc = NULL;
+  BfCudaStatus st = bfCudaFlattenEx(A, w->opts.flattenFlags, &desc);
+  BfCudaPlan *plan = NULL;
+  if (st == BF_CUDA_OK) {
+    desc->device = w->opts.device;
+    desc->buildTranspose = w->opts.buildTranspose;
+    st = bfCudaPlanCreate(desc, &plan);
+    bfCudaFlattenFree(desc);
+  }
+  if (st == BF_CUDA_OK && (w->inPerm || w->outPerm)) st = bfCudaPlanSetPerms(plan, w->inPerm, w->outPerm);
+  if (st != BF_CUDA_OK) {
+    bfCudaPlanDestroy(plan);
+    bfSetError(BF_ERROR_RUNTIME_ERROR);
+    return 0;
+  }
+  bfCudaPlanDestroy(w->plan);
+  w->plan = plan;
+  w->dirty = 0;
+  w->transposed = 0; /* the new snapshot is of the object as it stands */
+  return 1;
+}
+
+/* Direction of the plan that bfMatMul / bfMatMulVec mean right now. */
+static int forwardOp(Wrapper const *w) {
+  if (!w->transposed) return BF_CUDA_OP_N;
+  return w->dtype == BF_CUDA_COMPLEX_F64 ? BF_CUDA_OP_H : BF_CUDA_OP_T; /* src/mat_dense_complex.c:1475-1478 */
 }
 
 static enum BfError toBfError(BfCudaStatus st) {
@@ -46,6 +110,7 @@ static enum BfError toBfError(BfCudaStatus st) {
 
 /* Y = A X with X an n x nrhs BfMatDenseComplex (src/mat_block_dense.c:512, mat_product.c:211) */
 static BfMat *attachedMul(BfMat const *A, BfMat const *X) {
+  if (!refreshIfDirty(A)) return NULL;
   Wrapper *w = wrapperOf(A);
   if (w->dtype != BF_CUDA_COMPLEX_F64 || bfMatGetType(X) != BF_TYPE_MAT_DENSE_COMPLEX) {
     bfSetError(BF_ERROR_NOT_IMPLEMENTED);
@@ -64,7 +129,7 @@ static BfMat *attachedMul(BfMat const *A, BfMat const *X) {
   }
   BfMatDenseComplex *Y = bfMatDenseComplexNew();
   bfMatDenseComplexInit(Y, bfMatGetNumRows(A), nrhs);
-  BfCudaStatus st = bfCudaApplyHost(w->plan, BF_CUDA_OP_N, Xd->data, (int64_t)Xd->rowStride, (int64_t)nrhs,
+  BfCudaStatus st = bfCudaApplyHost(w->plan, forwardOp(w), Xd->data, (int64_t)Xd->rowStride, (int64_t)nrhs,
                                     Y->data, (int64_t)Y->rowStride);
   if (st != BF_CUDA_OK) {
     BfMat *Ym = bfMatDenseComplexToMat(Y);
@@ -77,6 +142,7 @@ static BfMat *attachedMul(BfMat const *A, BfMat const *X) {
 
 /* X A = (A^T X^T)^T (src/mat_product.c:282-310); X is p x numRows(A) */
 static BfMat *attachedRmul(BfMat const *A, BfMat const *X) {
+  if (!refreshIfDirty(A)) return NULL;
   Wrapper *w = wrapperOf(A);
   if (w->dtype != BF_CUDA_COMPLEX_F64 || bfMatGetType(X) != BF_TYPE_MAT_DENSE_COMPLEX) {
     bfSetError(BF_ERROR_NOT_IMPLEMENTED);
@@ -92,22 +158,28 @@ static BfMat *attachedRmul(BfMat const *A, BfMat const *X) {
     bfSetError(BF_ERROR_INVALID_ARGUMENTS); /* as src/mat_product.c:287-288 */
     return NULL;
   }
-  BfComplex *xt = malloc(sizeof(BfComplex) * (m * p ? m * p : 1));
-  BfComplex *yt = malloc(sizeof(BfComplex) * (n * p ? n * p : 1));
+  BfComplex *xt = malloc(sizeof(BfComplex) * (m * p > 0 ? m * p : 1));
+  BfComplex *yt = malloc(sizeof(BfComplex) * (n * p > 0 ? n * p : 1));
   if (!xt || !yt) {
     free(xt); free(yt);
     bfSetError(BF_ERROR_MEMORY_ERROR);
     return NULL;
   }
+  /* after bfMatTranspose the object is A0^H (A0 = the snapshot), so X A = (conj(A0) X^T)^T =
+   * conj(A0 conj(X^T))^T: the forward direction between two conjugations */
+  const int cj = w->transposed;
   for (BfSize i = 0; i < p; ++i)
-    for (BfSize j = 0; j < m; ++j) xt[j * p + i] = Xd->data[i * Xd->rowStride + j];
-  BfCudaStatus st = bfCudaApplyHost(w->plan, BF_CUDA_OP_T, xt, (int64_t)p, (int64_t)p, yt, (int64_t)p);
+    for (BfSize j = 0; j < m; ++j) {
+      BfComplex v = Xd->data[i * Xd->rowStride + j];
+      xt[j * p + i] = cj ? conj(v) : v;
+    }
+  BfCudaStatus st = bfCudaApplyHost(w->plan, cj ? BF_CUDA_OP_N : BF_CUDA_OP_T, xt, (int64_t)p, (int64_t)p, yt, (int64_t)p);
   BfMat *result = NULL;
   if (st == BF_CUDA_OK) {
     BfMatDenseComplex *Y = bfMatDenseComplexNew();
     bfMatDenseComplexInit(Y, p, n);
     for (BfSize i = 0; i < p; ++i)
-      for (BfSize j = 0; j < n; ++j) Y->data[i * Y->rowStride + j] = yt[j * p + i];
+      for (BfSize j = 0; j < n; ++j) Y->data[i * Y->rowStride + j] = cj ? conj(yt[j * p + i]) : yt[j * p + i];
     result = bfMatDenseComplexToMat(Y);
   } else {
     bfSetError(toBfError(st));
@@ -116,17 +188,21 @@ static BfMat *attachedRmul(BfMat const *A, BfMat const *X) {
   return result;
 }
 
-static BfVec *applyVec(BfMat const *A, BfVec const *x, int op) {
+/* rmul = 0: y = A x (MulVec); rmul = 1: y = A^T x (RmulVec, src/mat_product.c:312-345). */
+static BfVec *applyVec(BfMat const *A, BfVec const *x, int rmul) {
+  if (!refreshIfDirty(A)) return NULL;
   Wrapper *w = wrapperOf(A);
   BfType type = bfVecGetType(x);
-  BfSize nIn = op == BF_CUDA_OP_N ? bfMatGetNumCols(A) : bfMatGetNumRows(A);
-  BfSize nOut = op == BF_CUDA_OP_N ? bfMatGetNumRows(A) : bfMatGetNumCols(A);
+  BfSize nIn = rmul ? bfMatGetNumRows(A) : bfMatGetNumCols(A);
+  BfSize nOut = rmul ? bfMatGetNumCols(A) : bfMatGetNumRows(A);
   if (x->size != nIn) {
     bfSetError(BF_ERROR_INCOMPATIBLE_SHAPES);
     return NULL;
   }
   if (w->dtype == BF_CUDA_REAL_F64 && type == BF_TYPE_VEC_REAL) {
-    /* the only operand type the reference's block MulVec accepts, src/mat_block_diag.c:418-428 */
+    /* the only operand type the reference's block MulVec accepts, src/mat_block_diag.c:418-428;
+     * real: Transpose is the plain transpose, so a transposed object simply swaps the directions */
+    int op = (rmul != 0) != (w->transposed != 0) ? BF_CUDA_OP_T : BF_CUDA_OP_N;
     BfVecReal const *xr = bfVecConstToVecRealConst(x);
     BfVecReal *y = bfVecRealNewEmpty(nOut);
     BfCudaStatus st = bfCudaApplyHost(w->plan, op, xr->data, (int64_t)xr->stride, 1, y->data, (int64_t)y->stride);
@@ -139,10 +215,27 @@ static BfVec *applyVec(BfMat const *A, BfVec const *x, int op) {
     return bfVecRealToVec(y);
   }
   if (w->dtype == BF_CUDA_COMPLEX_F64 && type == BF_TYPE_VEC_COMPLEX) {
+    /* EXTENSION: the reference's block types raise NOT_IMPLEMENTED for a BfVecComplex operand
+     * (src/mat_block_diag.c:418-428, src/mat_block_dense.c:586-592), i.e. a reference program cannot
+     * reach this branch without aborting; the attached object answers with the product instead
+     * (== bfMatMul with a one-column BfMatDenseComplex; pinned by tests/test_gpu_attach_slots.py).
+     * A transposed object is A0^H: MulVec = OP_H; RmulVec = (A0^H)^T x = conj(A0 conj(x)). */
     BfVecComplex const *xc = bfVecConstToVecComplexConst(x);
     BfVecComplex *y = bfVecComplexNew();
     bfVecComplexInit(y, nOut);
-    BfCudaStatus st = bfCudaApplyHost(w->plan, op, xc->data, (int64_t)xc->stride, 1, y->data, (int64_t)y->stride);
+    int op = rmul ? (w->transposed ? BF_CUDA_OP_N : BF_CUDA_OP_T) : forwardOp(w);
+    const int cj = rmul && w->transposed;
+    BfComplex *tmp = NULL;
+    BfCudaStatus st;
+    if (cj) {
+      tmp = malloc(sizeof(BfComplex) * (nIn ? nIn : 1));
+      for (BfSize i = 0; i < nIn; ++i) tmp[i] = conj(xc->data[i * xc->stride]);
+      st = bfCudaApplyHost(w->plan, op, tmp, 1, 1, y->data, (int64_t)y->stride);
+      for (BfSize i = 0; i < nOut; ++i) y->data[i * y->stride] = conj(y->data[i * y->stride]);
+      free(tmp);
+    } else {
+      st = bfCudaApplyHost(w->plan, op, xc->data, (int64_t)xc->stride, 1, y->data, (int64_t)y->stride);
+    }
     if (st != BF_CUDA_OK) {
       BfVec *yv = bfVecComplexToVec(y);
       bfVecDelete(&yv);
@@ -155,27 +248,86 @@ static BfVec *applyVec(BfMat const *A, BfVec const *x, int op) {
   return NULL;
 }
 
-static BfVec *attachedMulVec(BfMat const *A, BfVec const *x) { return applyVec(A, x, BF_CUDA_OP_N); }
-static BfVec *attachedRmulVec(BfMat const *A, BfVec const *x) { return applyVec(A, x, BF_CUDA_OP_T); }
+static BfVec *attachedMulVec(BfMat const *A, BfVec const *x) { return applyVec(A, x, 0); }
+static BfVec *attachedRmulVec(BfMat const *A, BfVec const *x) { return applyVec(A, x, 1); }
 
 static BfSize attachedNumBytes(BfMat const *A) {
   Wrapper *w = wrapperOf(A);
-  BfMat *B = (BfMat *)A;
-  BfMatVtable *mine = B->vtbl;
-  B->vtbl = w->orig;
-  BfSize n = bfMatNumBytes(A);
-  B->vtbl = mine;
+  BfSize n = 0;
+  WITH_ORIG_VTABLE(A, w, n = bfMatNumBytes(A));
   return n;
 }
 
 static void attachedDelete(BfMat **A) {
   Wrapper *w = wrapperOf(*A);
   (*A)->vtbl = w->orig;
-  bfCudaPlanDestroy(w->plan);
-  w->magic = 0;
-  free(w);
+  /* A view never owns the plan.  (bfMatGetView / bfMatCopy on an attached object go through the
+   * overrides below and hand out objects with the original vtable; a view that carries the swapped
+   * pointer can only come from a typed constructor called directly, e.g. bfMatProductGetView.) */
+  if (!((*A)->props & BF_MAT_PROPS_VIEW)) freeWrapper(w);
   bfMatDelete(A);
 }
+
+/* ---- slots that alias the object: hand out plain reference objects ------------------------------ */
+static BfMat *attachedGetView(BfMat *A) {
+  BfMat *V = NULL;
+  WITH_ORIG_VTABLE(A, wrapperOf(A), V = bfMatGetView(A));
+  return V;
+}
+static BfMat *attachedCopy(BfMat const *A) {
+  Wrapper *w = wrapperOf(A);
+  if (w->valueless) { /* no host values to copy */
+    bfSetError(BF_ERROR_NOT_IMPLEMENTED);
+    return NULL;
+  }
+  BfMat *C = NULL;
+  WITH_ORIG_VTABLE(A, w, C = bfMatCopy(A));
+  return C;
+}
+
+/* ---- slots that edit the object in place ----------------------------------------------------------
+ * The edit is made by the reference's own code on the host object; the snapshot is marked stale and
+ * retaken by the next apply (refreshIfDirty).  bfMatTranspose is the cheap exception: when the
+ * reverse direction was compiled the plan already holds it (reversed factor order + transposed
+ * leaves is exactly what bfMatProductTranspose builds, src/mat_product.c:409-424), so only a flag
+ * flips.  An operator attached through a helm2 recording has no host values to edit or re-flatten. */
+static int beginEdit(BfMat *A) {
+  Wrapper *w = wrapperOf(A);
+  if (w->valueless) {
+    bfSetError(BF_ERROR_NOT_IMPLEMENTED);
+    return 0;
+  }
+  w->dirty = 1;
+  return 1;
+}
+static void attachedTranspose(BfMat *A) {
+  Wrapper *w = wrapperOf(A);
+  const int need = w->dtype == BF_CUDA_COMPLEX_F64 ? 2 : 1;
+  if (!w->dirty && (w->opts.buildTranspose & need)) {
+    w->transposed ^= 1;
+  } else if (!beginEdit(A)) {
+    return;
+  }
+  WITH_ORIG_VTABLE(A, w, bfMatTranspose(A));
+}
+static void attachedScale(BfMat *A, BfComplex c) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatScale(A, c)); }
+static void attachedScaleRows(BfMat *A, BfVec const *v) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatScaleRows(A, v)); }
+static void attachedScaleCols(BfMat *A, BfVec const *v) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatScaleCols(A, v)); }
+static void attachedDivideCols(BfMat *A, BfVec const *v) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatDivideCols(A, v)); }
+static void attachedAddInplace(BfMat *A, BfMat const *B) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatAddInplace(A, B)); }
+static void attachedSubInplace(BfMat *A, BfMat const *B) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatSubInplace(A, B)); }
+static void attachedAddDiag(BfMat *A, BfMat const *B) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatAddDiag(A, B)); }
+static void attachedNegate(BfMat *A) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatNegate(A)); }
+static void attachedSetRow(BfMat *A, BfSize i, BfVec const *v) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatSetRow(A, i, v)); }
+static void attachedSetCol(BfMat *A, BfSize j, BfVec const *v) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatSetCol(A, j, v)); }
+static void attachedSetColRange(BfMat *A, BfSize j, BfSize i0, BfSize i1, BfVec const *v) {
+  if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatSetColRange(A, j, i0, i1, v));
+}
+static void attachedSetRowRange(BfMat *A, BfSize i0, BfSize i1, BfMat const *B) {
+  if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatSetRowRange(A, i0, i1, B));
+}
+static void attachedPermuteRows(BfMat *A, BfPerm const *p) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatPermuteRows(A, p)); }
+static void attachedPermuteCols(BfMat *A, BfPerm const *p) { if (beginEdit(A)) WITH_ORIG_VTABLE(A, wrapperOf(A), bfMatPermuteCols(A, p)); }
 
 static int isAttached(BfMat const *A) {
   /* an attached vtable pointer is the address of a heap Wrapper whose Mul slot is ours */
@@ -220,14 +372,37 @@ static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHel
   w->plan = plan;
   w->dtype = dtype;
   w->magic = WRAPPER_MAGIC;
+  if (opts) w->opts = *opts;
+  else w->opts.device = -1;
+  w->valueless = rec != NULL;
   w->vt.Mul = attachedMul;
   w->vt.MulVec = attachedMulVec;
   w->vt.Rmul = attachedRmul;
   w->vt.RmulVec = attachedRmulVec;
   /* slots the type leaves empty stay empty (MatSum has neither, src/mat_sum.c:12-17: such an object
-   * is freed with its own Deinit after bfCudaMatDetach) */
-  if (w->orig->NumBytes) w->vt.NumBytes = attachedNumBytes;
-  if (w->orig->Delete) w->vt.Delete = attachedDelete;
+   * is freed with its own Deinit after bfCudaMatDetach; calling an empty slot crashes in the
+   * reference too) */
+#define OVERRIDE(slot, fn) do { if (w->orig->slot) w->vt.slot = fn; } while (0)
+  OVERRIDE(NumBytes, attachedNumBytes);
+  OVERRIDE(Delete, attachedDelete);
+  OVERRIDE(GetView, attachedGetView);
+  OVERRIDE(Copy, attachedCopy);
+  OVERRIDE(Transpose, attachedTranspose);
+  OVERRIDE(Scale, attachedScale);
+  OVERRIDE(ScaleRows, attachedScaleRows);
+  OVERRIDE(ScaleCols, attachedScaleCols);
+  OVERRIDE(DivideCols, attachedDivideCols);
+  OVERRIDE(AddInplace, attachedAddInplace);
+  OVERRIDE(SubInplace, attachedSubInplace);
+  OVERRIDE(AddDiag, attachedAddDiag);
+  OVERRIDE(Negate, attachedNegate);
+  OVERRIDE(SetRow, attachedSetRow);
+  OVERRIDE(SetCol, attachedSetCol);
+  OVERRIDE(SetColRange, attachedSetColRange);
+  OVERRIDE(SetRowRange, attachedSetRowRange);
+  OVERRIDE(PermuteRows, attachedPermuteRows);
+  OVERRIDE(PermuteCols, attachedPermuteCols);
+#undef OVERRIDE
   A->vtbl = &w->vt;
   return BF_CUDA_OK;
 }
@@ -244,13 +419,25 @@ BfCudaStatus bfCudaMatDetach(BfMat *A) {
   if (!isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   Wrapper *w = wrapperOf(A);
   A->vtbl = w->orig;
-  bfCudaPlanDestroy(w->plan);
-  w->magic = 0;
-  free(w);
+  freeWrapper(w);
   return BF_CUDA_OK;
 }
 
-BfCudaPlan *bfCudaMatGetPlan(BfMat const *A) { return isAttached(A) ? wrapperOf(A)->plan : NULL; }
+/* The plan as a snapshot of the object as it stands NOW: refreshed after in-place edits, and re-taken
+ * (forward direction = the transposed object) if bfMatTranspose flipped it. */
+static BfCudaPlan *currentForwardPlan(BfMat const *A) {
+  Wrapper *w = wrapperOf(A);
+  if (w->transposed) {
+    if (w->valueless) {
+      bfSetError(BF_ERROR_NOT_IMPLEMENTED);
+      return NULL;
+    }
+    w->dirty = 1;
+  }
+  return refreshIfDirty(A) ? w->plan : NULL;
+}
+
+BfCudaPlan *bfCudaMatGetPlan(BfMat const *A) { return isAttached(A) ? currentForwardPlan(A) : NULL; }
 
 BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *outPerm) {
   if (!isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
@@ -268,6 +455,14 @@ BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *out
     st = BF_CUDA_ERROR_INCOMPATIBLE_SHAPES;
   else
     st = bfCudaPlanSetPerms(wrapperOf(A)->plan, in, out);
+  if (st == BF_CUDA_OK) { /* kept for refreshIfDirty */
+    Wrapper *w = wrapperOf(A);
+    free(w->inPerm);
+    free(w->outPerm);
+    w->inPerm = in;
+    w->outPerm = out;
+    return st;
+  }
   free(in);
   free(out);
   return st;
@@ -310,6 +505,8 @@ BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol
     return NULL;
   }
   BfSize n = bfMatGetNumRows(A);
+  BfCudaPlan *plan = currentForwardPlan(A);
+  if (plan == NULL) return NULL;
   BfMatDenseComplex const *Bd = bfMatConstToMatDenseComplexConst(B);
   BfMatDenseComplex const *X0d = X0 ? bfMatConstToMatDenseComplexConst(X0) : NULL;
   BfComplex *b = malloc(sizeof(BfComplex) * (n ? n : 1)), *x0 = NULL;
@@ -322,8 +519,8 @@ BfMat *bfCudaSolveGMRESMat(BfMat const *A, BfMat const *B, BfMat *X0, BfReal tol
   bfMatDenseComplexInit(X, n, 1);
   int64_t it = 0;
   BfCudaStatus st = M == NULL
-                        ? bfCudaSolveGMRES(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL, NULL)
-                        : bfCudaSolveGMRESPrecond(wrapperOf(A)->plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL,
+                        ? bfCudaSolveGMRES(plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL, NULL)
+                        : bfCudaSolveGMRESPrecond(plan, b, x0, tol, (int64_t)maxNumIter, X->data, &it, NULL,
                                                   NULL, solveWithM, (void *)M);
   free(b);
   free(x0);

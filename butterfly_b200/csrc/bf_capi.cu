@@ -98,6 +98,10 @@ BfCudaStatus bfCudaPlanDestroy(BfCudaPlan *P) {
   if (P->stream) cudaStreamSynchronize(P->stream);
   for (auto &d : P->dir) d.release();
   cudaFree(P->scratch); cudaFree(P->ioX); cudaFree(P->ioY);
+  for (int i = 0; i < 2; ++i) {
+    if (P->stage[i]) cudaFreeHost(P->stage[i]);
+    if (P->stageDone[i]) cudaEventDestroy(P->stageDone[i]);
+  }
   cudaFree(P->inPerm); cudaFree(P->outPerm); cudaFree(P->invInPerm); cudaFree(P->invOutPerm);
   for (cudaEvent_t e : P->events) cudaEventDestroy(e);
   if (P->stream) cudaStreamDestroy(P->stream);
@@ -123,7 +127,8 @@ BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **out) {
   if (!g.ok) return fail(BF_CUDA_ERROR_RUNTIME, "cudaSetDevice failed");
   cudaDeviceProp prop;
   BF_CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
-  if (prop.major < 10) return fail(BF_CUDA_ERROR_NO_DEVICE, "device is not sm_100-class; kernels are built for sm_100a only");
+  // sm_100a cubins run on compute capability 10.x only (an "a" target has no forward compatibility: sm_120 would fail at launch)
+  if (prop.major != 10) return fail(BF_CUDA_ERROR_NO_DEVICE, "device is not sm_100-class; kernels are built for sm_100a only");
   BF_CUDA_TRY(configureKernels());
 
   std::unique_ptr<BfCudaPlan> P(new BfCudaPlan());
@@ -360,6 +365,88 @@ BfCudaStatus bfCudaPlanGetWorkspace(BfCudaPlan *P, int32_t op, int64_t nrhs, voi
   return BF_CUDA_OK;
 }
 
+// ---- host-buffer apply ----------------------------------------------------------------------------
+// The reference hands us malloc'ed (pageable) BfMatDenseComplex::data / BfVecReal::data.  A
+// cudaMemcpyAsync from pageable memory is staged by the driver in small synchronous pieces; we stage it
+// ourselves instead: the operand is gathered (any ld) into one of two pinned buffers by the host while
+// the DMA engine moves the other one, and the result comes back the same way.  Buffers that are already
+// pinned (bench.py's e2e leg, a caller that registered its arrays) are copied directly.
+static bool hostPointerIsPinned(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+static BfCudaStatus ensureStage(BfCudaPlan *P) {
+  if (P->stage[0]) return BF_CUDA_OK;
+  for (int i = 0; i < 2; ++i) {
+    BF_CUDA_TRY(cudaHostAlloc(&P->stage[i], kStageBytes, cudaHostAllocDefault));
+    BF_CUDA_TRY(cudaEventCreateWithFlags(&P->stageDone[i], cudaEventDisableTiming));
+  }
+  return BF_CUDA_OK;
+}
+
+// rows x rowBytes block, host row stride hostPitch  <->  dense device block
+static BfCudaStatus stagedCopy(BfCudaPlan *P, unsigned char *dev, unsigned char *host, size_t hostPitch, size_t rowBytes,
+                               size_t rows, bool toDevice) {
+  if (rows == 0 || rowBytes == 0) return BF_CUDA_OK;
+  const bool dense = hostPitch == rowBytes;
+  if (hostPointerIsPinned(host)) {
+    if (dense) BF_CUDA_TRY(cudaMemcpyAsync(toDevice ? (void *)dev : (void *)host, toDevice ? (void *)host : (void *)dev, rows * rowBytes,
+                                           toDevice ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, P->stream));
+    else if (toDevice) BF_CUDA_TRY(cudaMemcpy2DAsync(dev, rowBytes, host, hostPitch, rowBytes, rows, cudaMemcpyHostToDevice, P->stream));
+    else BF_CUDA_TRY(cudaMemcpy2DAsync(host, hostPitch, dev, rowBytes, rowBytes, rows, cudaMemcpyDeviceToHost, P->stream));
+    return BF_CUDA_OK;
+  }
+  BfCudaStatus st = ensureStage(P);
+  if (st != BF_CUDA_OK) return st;
+  const size_t rowsPerChunk = std::max<size_t>(1, kStageBytes / rowBytes);
+  if (rowBytes > kStageBytes) { // absurdly wide rows: let the driver stage them
+    if (toDevice) BF_CUDA_TRY(cudaMemcpy2DAsync(dev, rowBytes, host, hostPitch, rowBytes, rows, cudaMemcpyHostToDevice, P->stream));
+    else BF_CUDA_TRY(cudaMemcpy2DAsync(host, hostPitch, dev, rowBytes, rowBytes, rows, cudaMemcpyDeviceToHost, P->stream));
+    return BF_CUDA_OK;
+  }
+  const size_t nChunks = (rows + rowsPerChunk - 1) / rowsPerChunk;
+  auto gather = [&](unsigned char *stage, size_t r0, size_t nr, bool in) {
+    if (dense) {
+      if (in) std::memcpy(stage, host + r0 * rowBytes, nr * rowBytes);
+      else std::memcpy(host + r0 * rowBytes, stage, nr * rowBytes);
+      return;
+    }
+    for (size_t r = 0; r < nr; ++r) {
+      if (in) std::memcpy(stage + r * rowBytes, host + (r0 + r) * hostPitch, rowBytes);
+      else std::memcpy(host + (r0 + r) * hostPitch, stage + r * rowBytes, rowBytes);
+    }
+  };
+  if (toDevice) {
+    for (size_t c = 0; c < nChunks; ++c) {
+      const int b = (int)(c & 1);
+      const size_t r0 = c * rowsPerChunk, nr = std::min(rowsPerChunk, rows - r0);
+      if (c >= 2) BF_CUDA_TRY(cudaEventSynchronize(P->stageDone[b])); // the DMA out of this buffer has finished
+      gather(P->stage[b], r0, nr, true);
+      BF_CUDA_TRY(cudaMemcpyAsync(dev + r0 * rowBytes, P->stage[b], nr * rowBytes, cudaMemcpyHostToDevice, P->stream));
+      BF_CUDA_TRY(cudaEventRecord(P->stageDone[b], P->stream));
+    }
+  } else {
+    // chunk c + 1 is in flight while the host scatters chunk c
+    auto issue = [&](size_t c) -> cudaError_t {
+      const int b = (int)(c & 1);
+      const size_t r0 = c * rowsPerChunk, nr = std::min(rowsPerChunk, rows - r0);
+      cudaError_t e = cudaMemcpyAsync(P->stage[b], dev + r0 * rowBytes, nr * rowBytes, cudaMemcpyDeviceToHost, P->stream);
+      return e == cudaSuccess ? cudaEventRecord(P->stageDone[b], P->stream) : e;
+    };
+    BF_CUDA_TRY(issue(0));
+    for (size_t c = 0; c < nChunks; ++c) {
+      const int b = (int)(c & 1);
+      const size_t r0 = c * rowsPerChunk, nr = std::min(rowsPerChunk, rows - r0);
+      if (c + 1 < nChunks) BF_CUDA_TRY(issue(c + 1));
+      BF_CUDA_TRY(cudaEventSynchronize(P->stageDone[b]));
+      gather(P->stage[b], r0, nr, false);
+    }
+  }
+  return BF_CUDA_OK;
+}
+
 BfCudaStatus bfCudaApplyHost(BfCudaPlan *P, int32_t op, const void *x, int64_t ldx, int64_t nrhs, void *y,
                              int64_t ldy) {
   if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
@@ -375,18 +462,15 @@ BfCudaStatus bfCudaApplyHost(BfCudaPlan *P, int32_t op, const void *x, int64_t l
   if (st != BF_CUDA_OK) return st;
   st = ensureBytes(&P->ioY, &P->ioYBytes, std::max<size_t>((size_t)D.rowsOut * rowBytes, 16));
   if (st != BF_CUDA_OK) return st;
-  // dense operands (ld == nrhs, the reference's own layout: rowStride == numCols) move as ONE linear
-  // copy; a 2-D copy of 16-byte rows runs at a fraction of PCIe bandwidth
-  if (D.rowsIn > 0) {
-    if (ldx == nrhs) BF_CUDA_TRY(cudaMemcpyAsync(P->ioX, x, (size_t)D.rowsIn * rowBytes, cudaMemcpyHostToDevice, P->stream));
-    else BF_CUDA_TRY(cudaMemcpy2DAsync(P->ioX, rowBytes, x, (size_t)ldx * es, rowBytes, (size_t)D.rowsIn, cudaMemcpyHostToDevice, P->stream));
-  }
+  // the device copies are always dense (ld == nrhs): strided operands (BfVec views, padded row strides)
+  // are gathered on the host side of the copy
+  st = stagedCopy(P, P->ioX, const_cast<unsigned char *>(static_cast<const unsigned char *>(x)), (size_t)ldx * es, rowBytes,
+                  (size_t)D.rowsIn, true);
+  if (st != BF_CUDA_OK) return st;
   st = bfCudaApplyDevice(P, op, P->ioX, nrhs, nrhs, P->ioY, nrhs, P->stream);
   if (st != BF_CUDA_OK) return st;
-  if (D.rowsOut > 0) {
-    if (ldy == nrhs) BF_CUDA_TRY(cudaMemcpyAsync(y, P->ioY, (size_t)D.rowsOut * rowBytes, cudaMemcpyDeviceToHost, P->stream));
-    else BF_CUDA_TRY(cudaMemcpy2DAsync(y, (size_t)ldy * es, P->ioY, rowBytes, rowBytes, (size_t)D.rowsOut, cudaMemcpyDeviceToHost, P->stream));
-  }
+  st = stagedCopy(P, P->ioY, static_cast<unsigned char *>(y), (size_t)ldy * es, rowBytes, (size_t)D.rowsOut, false);
+  if (st != BF_CUDA_OK) return st;
   BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
   return BF_CUDA_OK;
 }

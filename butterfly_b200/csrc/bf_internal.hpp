@@ -56,6 +56,8 @@ struct DevDirection {
 };
 } // namespace bfc
 
+constexpr size_t kStageBytes = size_t(8) << 20; // one pinned staging buffer
+
 struct BfCudaPlan {
   int device = 0;
   int numSMs = 148;
@@ -69,6 +71,9 @@ struct BfCudaPlan {
   // host-API I/O buffers
   unsigned char *ioX = nullptr, *ioY = nullptr;
   size_t ioXBytes = 0, ioYBytes = 0;
+  // pinned double buffer between pageable caller memory and ioX / ioY (bfCudaApplyHost)
+  unsigned char *stage[2] = {nullptr, nullptr};
+  cudaEvent_t stageDone[2] = {nullptr, nullptr};
   // fused caller-side permutations (scatter form) and their inverses
   int32_t *inPerm = nullptr, *outPerm = nullptr, *invInPerm = nullptr, *invOutPerm = nullptr;
   int64_t lastLaunches = 0;

@@ -153,11 +153,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   }
   __syncthreads();
 
+  // Under programmatic dependent launch EVERY exit path runs griddepcontrol.wait first: stage-to-stage
+  // ordering is transitive only through grids whose threads all waited, and a stage with no local items
+  // (a row-sharded plan whose leaves of that stage are all remote) must not let stage s + 1 overtake s - 1.
+  auto pdlSync = [&]() {
+    if (a.pdl) {
+      asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+  };
   const int q = blockIdx.x * kWarpsPerCta + warp;
-  if (q >= a.numQueues) return;
+  if (q >= a.numQueues) { pdlSync(); return; }
   const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
   const uint32_t tBeg = a.qTileBegin[q], tEnd = a.qTileBegin[q + 1];
-  if (iBeg == iEnd) return;
+  if (iBeg == iEnd) { pdlSync(); return; }
   const uint64_t pol = policyEvictFirst();
 
   // Descriptor windows: lane l holds tiles[twBase + l] / tiles[twBase + 32 + l] (and the same for
@@ -241,10 +250,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   // wait.  With one 222 KiB CTA per SM the overlap is the prologue of a CTA on an SM the previous stage has
   // already left.  Measured A/B: 0.175 -> 0.165 ms per apply at N = 16 384, 0.630 -> 0.608 at 65 536, but
   // 10.67 -> 10.85 ms at N = 524 288 — hence the size switch.
-  if (a.pdl) {
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-  }
+  pdlSync();
 #pragma unroll 1
   for (int s = 0; s < kGemvSlots; ++s) produce();
 

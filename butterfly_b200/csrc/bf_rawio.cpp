@@ -44,6 +44,13 @@ extern "C" {
 BfCudaStatus bfCudaRawOpsSave(const BfCudaPlanDesc *d, const char *path) {
   if (!d || !path) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   const bool cplx = d->dtype == BF_CUDA_COMPLEX_F64;
+  // A value-less dense / diagonal leaf (an operator whose values were built on the GPU) would reload as
+  // a silent all-zero block: refuse.  Such operators are persisted as compiled plans (bfCudaPlanSave).
+  for (int64_t i = 0; i < d->numOps; ++i) {
+    const BfCudaRawOp &o = d->ops[i];
+    if ((o.kind == BF_CUDA_LEAF_DENSE || o.kind == BF_CUDA_LEAF_DIAG) && o.m > 0 && o.k > 0 && !o.val)
+      return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  }
   FILE *fp = std::fopen(path, "wb");
   if (!fp) return BF_CUDA_ERROR_IO;
   Header h{};
@@ -89,9 +96,23 @@ BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **out) {
   if (!fp) return BF_CUDA_ERROR_IO;
   Header h;
   if (std::fread(&h, sizeof h, 1, fp) != 1 || std::memcmp(h.magic, "BFRAWOP1", 8) != 0 || h.numBufs < 2 ||
-      h.numOps < 0 || h.numValueDoubles < 0) {
+      h.numOps < 0 || h.numValueDoubles < 0 || (h.dtype != BF_CUDA_REAL_F64 && h.dtype != BF_CUDA_COMPLEX_F64)) {
     std::fclose(fp);
     return BF_CUDA_ERROR_IO;
+  }
+  // every count is bounded by what the file can hold (a corrupt header must not size a malloc)
+  {
+    long cur = std::ftell(fp);
+    std::fseek(fp, 0, SEEK_END);
+    const long end = std::ftell(fp);
+    std::fseek(fp, cur, SEEK_SET);
+    const uint64_t avail = end > cur ? (uint64_t)(end - cur) : 0;
+    const uint64_t nb = (uint64_t)h.numBufs, no = (uint64_t)h.numOps, nv = (uint64_t)h.numValueDoubles;
+    if (nb > avail / 8 || no > avail / sizeof(BfCudaRawOp) || nv > avail / 8 ||
+        nb * 8 + no * sizeof(BfCudaRawOp) + nv * 8 != avail) {
+      std::fclose(fp);
+      return BF_CUDA_ERROR_IO;
+    }
   }
   const size_t szDesc = (sizeof(BfCudaPlanDesc) + 15) & ~size_t(15);
   const size_t szBufs = ((size_t)h.numBufs * 8 + 15) & ~size_t(15);
@@ -107,11 +128,24 @@ BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **out) {
   ok = ok && (h.numOps == 0 || std::fread(ops, sizeof(BfCudaRawOp), (size_t)h.numOps, fp) == (size_t)h.numOps);
   ok = ok && (szVals == 0 || std::fread(vals, 1, szVals, fp) == szVals);
   std::fclose(fp);
+  const bool cplx = h.dtype == BF_CUDA_COMPLEX_F64;
+  for (int64_t i = 0; ok && i < h.numBufs; ++i) ok = bufRows[i] >= 0;
   for (int64_t i = 0; ok && i < h.numOps; ++i) {
-    const intptr_t off = (intptr_t)ops[i].val;
-    if (off == -1) ops[i].val = nullptr;
-    else if (off < 0 || off >= h.numValueDoubles) ok = false;
-    else ops[i].val = vals + off;
+    BfCudaRawOp &o = ops[i];
+    const intptr_t off = (intptr_t)o.val;
+    o.val = nullptr;
+    // shape and placement must be sane before the leaf's extent can be computed at all
+    if (o.m < 0 || o.k < 0 || o.m > (int64_t(1) << 40) || o.k > (int64_t(1) << 40) || o.inBuf < 0 || o.inBuf >= h.numBufs ||
+        o.outBuf < 0 || o.outBuf >= h.numBufs || o.inOff < 0 || o.outOff < 0 ||
+        (o.kind != BF_CUDA_LEAF_DENSE && o.kind != BF_CUDA_LEAF_IDENTITY && o.kind != BF_CUDA_LEAF_DIAG)) { ok = false; break; }
+    if (off == -1) continue;
+    o.val = vals; // non-null so that leafDoubles counts it
+    int64_t sr, sc;
+    storedShape(o, cplx, &sr, &sc);
+    const int64_t need = leafDoubles(o, cplx);
+    if (off < 0 || need > h.numValueDoubles || off > h.numValueDoubles - need ||
+        (o.kind == BF_CUDA_LEAF_DENSE && o.ld != sc)) { ok = false; break; }
+    o.val = vals + off;
   }
   if (!ok) { std::free(arena); return BF_CUDA_ERROR_IO; }
   std::memset(d, 0, sizeof *d);

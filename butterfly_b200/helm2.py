@@ -14,6 +14,30 @@ from .rawops import RawOps  # noqa: F401 (re-exported)
 
 HELM2_LIB_PATH = capi.LIB_DIR / "libbfcuda_helm2.so"
 
+_recorder = None
+
+
+def load_recorder() -> C.CDLL:
+    """dlopen libbfcuda_helm2.so (csrc/bf_helm2_record.c) into the GLOBAL symbol scope.  It must be loaded
+    BEFORE libbutterfly so that its bfHelm2GetKernelMatrix / bfHelm2GetReexpansionMatrix win, and it has no
+    link-time dependency on any particular libbutterfly (the three bf* functions it calls are bound on first
+    use) — exactly what `-lbfcuda_helm2 -lbutterfly` gives a C program.  ctypes.CDLL forces RTLD_NOW, which
+    would need those symbols at load time, hence the direct dlopen with RTLD_LAZY."""
+    global _recorder
+    if _recorder is None:
+        import os
+
+        libc = C.CDLL(None)
+        libc.dlopen.restype = C.c_void_p
+        libc.dlopen.argtypes = [C.c_char_p, C.c_int]
+        libc.dlerror.restype = C.c_char_p
+        handle = libc.dlopen(str(HELM2_LIB_PATH).encode(), os.RTLD_LAZY | os.RTLD_GLOBAL)
+        if not handle:
+            raise OSError(f"dlopen({HELM2_LIB_PATH}): {(libc.dlerror() or b'').decode()}")
+        _recorder = C.CDLL(str(HELM2_LIB_PATH), handle=handle)
+    return _recorder
+
+
 KERNEL, REEXPANSION = 0, 1
 LAYER_POT_SINGLE, LAYER_POT_PV_DOUBLE, LAYER_POT_PV_NORMAL_DERIV_SINGLE, LAYER_POT_COMBINED_FIELD = 1, 2, 3, 5
 

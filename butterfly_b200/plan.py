@@ -27,10 +27,25 @@ class Plan:
         self.handle = h
         self._info = None
 
+    @classmethod
+    def borrow(cls, handle, num_rows: int, num_cols: int, dtype: int = capi.COMPLEX_F64) -> "Plan":
+        """A handle on a plan somebody else owns (bfCudaMatGetPlan of an attached reference object):
+        same methods, never destroyed from here."""
+        self = cls.__new__(cls)
+        self.lib = capi.load_library()
+        self.raw = type("Shape", (), {"num_rows": int(num_rows), "num_cols": int(num_cols), "dtype": dtype})()
+        self.dtype = dtype
+        self.np_dtype = np.complex128 if dtype == capi.COMPLEX_F64 else np.float64
+        self.handle = C.c_void_p(handle) if not isinstance(handle, C.c_void_p) else handle
+        self._info = None
+        self._borrowed = True
+        return self
+
     # ------------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "handle", None):
-            self.lib.bfCudaPlanDestroy(self.handle)
+            if not getattr(self, "_borrowed", False):
+                self.lib.bfCudaPlanDestroy(self.handle)
             self.handle = None
 
     def __del__(self):

@@ -16,6 +16,7 @@
 #include <bf/layer_pot.h>
 #include <bf/linalg.h>
 #include <bf/lu.h>
+#include <bf/mat_block_dense.h>
 #include <bf/mat_block_diag.h>
 #include <bf/ptr_array.h>
 #include <complex.h>
@@ -398,3 +399,63 @@ double refCallGMRESPrecond(RefGmresFn fn, BfMat const *A, BfMat const *M, const 
   bfMatDelete(&Bm);
   return t1 - t0;
 }
+
+/* ---- the other public entry points of the apply path, for the attach-layer tests ------------------ */
+
+/* Y = bfMatRmul(A, X) = X A through the public vtable (src/mat.c:193; src/mat_product.c:282-310):
+ * X is p x m row-major complex (m = rows of A), Y is p x n.  Returns seconds inside bfMatRmul. */
+double refMatRmulComplex(BfMat const *A, const double *x, int64_t p, int64_t m, double *y) {
+  BfMatDenseComplex *X = bfMatDenseComplexNewViewFromPtr((BfSize)p, (BfSize)m, (BfComplex *)x);
+  double t0 = refNow();
+  BfMat *Y = bfMatRmul(A, bfMatDenseComplexToMat(X));
+  double t1 = refNow();
+  BfMatDenseComplex *Yd = bfMatToMatDenseComplex(Y);
+  BfSize n = bfMatGetNumCols(Y);
+  for (BfSize i = 0; i < (BfSize)p; ++i)
+    memcpy(y + 2 * i * n, Yd->data + i * Yd->rowStride, sizeof(BfComplex) * (size_t)n);
+  bfMatDelete(&Y);
+  BfMat *Xm = bfMatDenseComplexToMat(X);
+  bfMatDelete(&Xm);
+  return t1 - t0;
+}
+
+/* bfMatMulVec / bfMatRmulVec with a STRIDED BfVecReal view (bfVecRealInitView, include/bf/vec_real.h:48):
+ * element i of the operand is x[i * stride]. */
+double refMatMulVecRealStrided(BfMat const *A, const double *x, int64_t n, int64_t stride, double *y, int transposed) {
+  BfVecReal *xv = bfVecRealNew();
+  bfVecRealInitView(xv, (BfSize)n, (BfSize)stride, (BfReal *)x);
+  double t0 = refNow();
+  BfVec *yv = transposed ? bfMatRmulVec(A, bfVecRealToVec(xv)) : bfMatMulVec(A, bfVecRealToVec(xv));
+  double t1 = refNow();
+  BfVecReal *yr = bfVecToVecReal(yv);
+  for (BfSize i = 0; i < yv->size; ++i) y[i] = yr->data[i * yr->stride];
+  bfVecDelete(&yv);
+  BfVec *xvv = bfVecRealToVec(xv);
+  bfVecDelete(&xvv);
+  return t1 - t0;
+}
+
+/* bfMatMulVec / bfMatRmulVec with a (strided) BfVecComplex view.  The reference's block types refuse this
+ * operand type (src/mat_block_diag.c:418-428): only call it on an ATTACHED object. */
+double refMatMulVecComplexStrided(BfMat const *A, const double *x, int64_t n, int64_t stride, double *y, int transposed) {
+  BfVecComplex *xv = bfVecComplexNew();
+  bfVecComplexInitView(xv, (BfSize)n, (BfSize)stride, (BfComplex *)x);
+  double t0 = refNow();
+  BfVec *yv = transposed ? bfMatRmulVec(A, bfVecComplexToVec(xv)) : bfMatMulVec(A, bfVecComplexToVec(xv));
+  double t1 = refNow();
+  if (yv == NULL) return -1.0;
+  BfVecComplex *yc = bfVecToVecComplex(yv);
+  for (BfSize i = 0; i < yv->size; ++i) ((BfComplex *)y)[i] = yc->data[i * yc->stride];
+  bfVecDelete(&yv);
+  BfVec *xvv = bfVecComplexToVec(xv);
+  bfVecDelete(&xvv);
+  return t1 - t0;
+}
+
+/* aliasing slots: bfMatGet(A, BF_POLICY_VIEW) as multiple_scattering_context.c:616 takes it, bfMatCopy, bfMatDelete */
+BfMat *refMatGetView(BfMat *A) { return bfMatGetView(A); }
+BfMat *refMatCopy(BfMat const *A) { return bfMatCopy(A); }
+void refMatDelete(BfMat *A) { bfMatDelete(&A); }
+/* the typed view constructor called directly (bypasses the vtable): the view is a struct copy of the owner */
+BfMat *refMatBlockDenseGetViewDirect(BfMat *A) { return bfMatBlockDenseGetView((BfMatBlockDense *)A); }
+void refHelm2SetMat(RefHelm2 *h, BfMat *A) { h->A = A; }

@@ -57,6 +57,14 @@ def load():
         d.refHelm2MakeSecondKind.argtypes = [vp, dbl]; d.refHelm2MakeSecondKind.restype = None
         d.refSolveGMRES.argtypes = [vp, vp, i64, dbl, i64, vp, vp]; d.refSolveGMRES.restype = dbl
         d.refCallGMRES.argtypes = [vp, vp, vp, i64, dbl, i64, vp, vp]; d.refCallGMRES.restype = dbl
+        d.refMatRmulComplex.argtypes = [vp, vp, i64, i64, vp]; d.refMatRmulComplex.restype = dbl
+        d.refMatMulVecRealStrided.argtypes = [vp, vp, i64, i64, vp, C.c_int]; d.refMatMulVecRealStrided.restype = dbl
+        d.refMatMulVecComplexStrided.argtypes = [vp, vp, i64, i64, vp, C.c_int]; d.refMatMulVecComplexStrided.restype = dbl
+        d.refMatGetView.argtypes = [vp]; d.refMatGetView.restype = vp
+        d.refMatBlockDenseGetViewDirect.argtypes = [vp]; d.refMatBlockDenseGetViewDirect.restype = vp
+        d.refMatCopy.argtypes = [vp]; d.refMatCopy.restype = vp
+        d.refMatDelete.argtypes = [vp]; d.refMatDelete.restype = None
+        d.refMatTranspose.argtypes = [vp]; d.refMatTranspose.restype = None
         _drv = d
     return _drv
 
@@ -123,6 +131,50 @@ class Helm2:
         y = np.zeros((self.drv.refMatNumRows(self.mat), x.shape[1]), np.complex128)
         t = self.drv.refMatMulComplex(self.mat, x.ctypes.data, x.shape[0], x.shape[1], y.ctypes.data)
         return y, t
+
+    def rmul(self, x: np.ndarray, mat=None):
+        """bfMatRmul(A, X) = X A through the CURRENT vtable (src/mat_product.c:282-310); X is p x numRows(A)."""
+        mat = mat or self.mat
+        x = np.ascontiguousarray(x, dtype=np.complex128)
+        y = np.zeros((x.shape[0], self.drv.refMatNumCols(mat)), np.complex128)
+        t = self.drv.refMatRmulComplex(mat, x.ctypes.data, x.shape[0], x.shape[1], y.ctypes.data)
+        return y, t
+
+    def matmul_on(self, mat, x: np.ndarray):
+        """bfMatMul on another BfMat* of the same shape (a view or a copy of this operator)."""
+        x = np.ascontiguousarray(x, dtype=np.complex128)
+        if x.ndim == 1:
+            x = x[:, None]
+        y = np.zeros((self.drv.refMatNumRows(mat), x.shape[1]), np.complex128)
+        self.drv.refMatMulComplex(mat, x.ctypes.data, x.shape[0], x.shape[1], y.ctypes.data)
+        return y
+
+    def mulvec_complex(self, x: np.ndarray, stride: int = 1, transposed: bool = False):
+        """bfMatMulVec / bfMatRmulVec with a BfVecComplex view of the given stride.  The reference's block
+        types refuse the operand type: only valid on an attached object."""
+        n = self.drv.refMatNumRows(self.mat) if transposed else self.drv.refMatNumCols(self.mat)
+        buf = np.zeros(n * stride, np.complex128)
+        buf[::stride] = x
+        y = np.zeros(self.drv.refMatNumCols(self.mat) if transposed else self.drv.refMatNumRows(self.mat), np.complex128)
+        t = self.drv.refMatMulVecComplexStrided(self.mat, buf.ctypes.data, n, stride, y.ctypes.data, int(transposed))
+        if t < 0:
+            raise RuntimeError("bfMatMulVec returned NULL")
+        return y
+
+    def transpose(self):
+        """bfMatTranspose in place (for complex leaves: the conjugate transpose, src/mat_dense_complex.c:1475-1478)."""
+        self.drv.refMatTranspose(self.mat)
+
+    def get_view(self, direct: bool = False):
+        """bfMatGetView(A) (what bfMatGet(A, BF_POLICY_VIEW) calls, multiple_scattering_context.c:616), or the
+        typed constructor bfMatBlockDenseGetView called directly (bypasses the vtable)."""
+        return self.drv.refMatBlockDenseGetViewDirect(self.mat) if direct else self.drv.refMatGetView(self.mat)
+
+    def copy(self):
+        return self.drv.refMatCopy(self.mat)
+
+    def delete_mat(self, mat):
+        self.drv.refMatDelete(mat)
 
     def make_second_kind(self, weight: float | None = None):
         """K <- K diag(w) + I/2 with the reference's own bfMatScaleCols / bfMatAddInplace
@@ -205,6 +257,13 @@ class Helm2:
         st = a.bfCudaMatAttach(self.mat, C.byref(o))
         if st != 0:
             raise capi.BfCudaError(st, "bfCudaMatAttach", capi.load_library().bfCudaLastErrorMessage().decode())
+
+    def plan_handle(self):
+        """bfCudaMatGetPlan: the plan behind the attached object (borrowed)."""
+        h = load_attach().bfCudaMatGetPlan(self.mat)
+        if not h:
+            raise RuntimeError("object is not attached")
+        return h
 
     def detach(self):
         st = load_attach().bfCudaMatDetach(self.mat)
@@ -321,6 +380,15 @@ class Stream:
         self.drv.refStreamGetRowPerm(self.h, p.ctypes.data)
         return p
 
+    def mulvec_strided(self, x: np.ndarray, stride: int, transposed: bool = False):
+        """The same calls with a BfVecReal VIEW of stride `stride` (bfVecRealInitView)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        buf = np.full(len(x) * stride, np.nan)
+        buf[::stride] = x
+        y = np.zeros(self.num_cols if transposed else self.num_rows)
+        t = self.drv.refMatMulVecRealStrided(self.mat, buf.ctypes.data, len(x), stride, y.ctypes.data, int(transposed))
+        return y, t
+
     def mulvec(self, x: np.ndarray, transposed: bool = False):
         """bfMatMulVec / bfMatRmulVec through the object's CURRENT vtable.  Returns (y, seconds)."""
         x = np.ascontiguousarray(x, dtype=np.float64)
@@ -331,6 +399,7 @@ class Stream:
     flatten = Helm2.flatten
     attach = Helm2.attach
     detach = Helm2.detach
+    plan_handle = Helm2.plan_handle
 
 
 def sphere_stream(n: int = 4000, lmax: int = 31, tol: float = 1e-3, freq_tree_depth: int = -1) -> "Stream":

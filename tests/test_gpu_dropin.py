@@ -60,6 +60,39 @@ def test_bfmatmul_through_swapped_vtable(n, k):
 
 
 @needs_ref
+def test_configs0_same_factors_cpu_vs_gpu():
+    """BASELINE.json configs[0] at its own size: fac_helm2 on 16 384 circle points, k = 400
+    (examples/simple/bf_all_blocks.c:96-147).  The reference builds the factors ONCE; its bfMatMul runs on
+    the CPU and, after bfCudaMatAttach, on the B200 — same factors, same operands — at 1, 64 and 256 RHS,
+    rel. l2 <= 1e-12 per column (north star)."""
+    n = 16384
+    h = reflib.Helm2(reflib.circle_points(n), 400.0)
+    try:
+        x = reflib.randn_complex(n, 0)
+        rng = np.random.default_rng(7)
+        X = rng.standard_normal((n, 256)) + 1j * rng.standard_normal((n, 256))
+        X[:, 0] = x
+        y_cpu, _ = h.matmul(x)
+        Y64_cpu, _ = h.matmul(X[:, :64].copy())
+        # 256 columns on one core take the reference ~10 s: the last 192 are checked on a spread of 24 of them
+        probe = np.arange(64, 256, 8)
+        Yp_cpu, _ = h.matmul(X[:, probe].copy())
+        h.attach()
+        y_gpu, _ = h.matmul(x)
+        Y64_gpu, _ = h.matmul(X[:, :64].copy())
+        Y256_gpu, _ = h.matmul(X)
+        h.detach()
+        assert np.linalg.norm(y_gpu - y_cpu) / np.linalg.norm(y_cpu) <= TOL
+        for c in range(64):
+            assert np.linalg.norm(Y64_gpu[:, c] - Y64_cpu[:, c]) / np.linalg.norm(Y64_cpu[:, c]) <= TOL
+            assert np.linalg.norm(Y256_gpu[:, c] - Y64_cpu[:, c]) / np.linalg.norm(Y64_cpu[:, c]) <= TOL
+        for i, c in enumerate(probe):
+            assert np.linalg.norm(Y256_gpu[:, c] - Yp_cpu[:, i]) / np.linalg.norm(Yp_cpu[:, i]) <= TOL
+    finally:
+        h.close()
+
+
+@needs_ref
 def test_corrected_system_matrix_through_swapped_vtable():
     """The multiple-scattering system matrix (multiple_scattering_context.c:456-487): Kapur-Rokhlin
     correction, column weights, + I/2, and a sparse MatCooComplex term in a MatSum next to the

@@ -67,6 +67,21 @@ def test_raw_ops_file_roundtrip(block, lib, tmp_path):
     assert np.array_equal(back.buf_rows, raw.buf_rows)
     assert np.array_equal(portlib.apply(back, x), portlib.apply(raw, x))
     assert lib.bfCudaRawOpsLoad(str(tmp_path / "missing").encode(), C.byref(out)) == 6  # BF_CUDA_ERROR_IO
+    # truncated and corrupted files are refused, not read out of bounds
+    blob = (tmp_path / "block.bfraw").read_bytes()
+    for bad in (blob[: len(blob) - 64], blob[: 56 + 8], blob + b"\0" * 8):
+        (tmp_path / "bad.bfraw").write_bytes(bad)
+        assert lib.bfCudaRawOpsLoad(str(tmp_path / "bad.bfraw").encode(), C.byref(out)) == 6
+    ops_at = 56 + 8 * len(raw.buf_rows)            # first RawOp; its `val` offset is the last 8 bytes of 72
+    forged = bytearray(blob)
+    forged[ops_at + 64 : ops_at + 72] = (2 ** 40).to_bytes(8, "little")
+    (tmp_path / "bad.bfraw").write_bytes(bytes(forged))
+    assert lib.bfCudaRawOpsLoad(str(tmp_path / "bad.bfraw").encode(), C.byref(out)) == 6
+    # a value-less dense leaf (GPU-built operator) would reload as zeros: Save refuses it
+    d2 = raw.desc()
+    ops = C.cast(d2.ops, C.POINTER(capi.RawOp))
+    ops[0].val = None
+    assert lib.bfCudaRawOpsSave(C.byref(d2), str(tmp_path / "noval.bfraw").encode()) == 1  # INVALID_ARGUMENT
 
 
 # ---- real (streamed, LBO-style) path: bfMatMulVec / bfMatRmulVec of the reference ----------------

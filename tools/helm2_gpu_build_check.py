@@ -27,7 +27,7 @@ def main():
 
     from butterfly_b200 import capi, helm2
 
-    rec_lib = C.CDLL(str(helm2.HELM2_LIB_PATH), mode=C.RTLD_GLOBAL)
+    rec_lib = helm2.load_recorder()
     from oracle import reflib
 
     att = reflib.load_attach()
@@ -104,6 +104,32 @@ def main():
         out["rel_l2_vs_reference"] = float(np.linalg.norm(y_gpu - y_ref) / np.linalg.norm(y_ref))
         if rows is not None:
             out["reference_vs_dense_rows"] = float(np.linalg.norm(y_ref[rows, 0] - want) / np.linalg.norm(want))
+        if "--same-factors" in sys.argv:
+            # the north star's own check at this N: the reference-built factors applied by the reference on the CPU
+            # and, after bfCudaMatAttach of THAT object, on the GPU — 1 RHS and a 256-RHS block (the block's columns
+            # checked against the CPU on a spread of 8 of them: 256 columns cost the reference about a minute)
+            att.bfCudaMatDetach(h.mat)  # the GPU-built operator's plan is no longer needed
+            rng = np.random.default_rng(9)
+            X256 = rng.standard_normal((n, 256)) + 1j * rng.standard_normal((n, 256))
+            probe = np.arange(5, 256, 32)
+            cpu_t = [h_ref.matmul(x)[1] for _ in range(3)]
+            Yp_ref, _ = h_ref.matmul(X256[:, probe].copy())
+            ta = time.time()
+            h_ref.attach()
+            out["reference_operator_attach_s"] = time.time() - ta
+            y_same, _ = h_ref.matmul(x)
+            gpu_t = [h_ref.matmul(x)[1] for _ in range(10)]
+            Y_same, t256 = h_ref.matmul(X256)
+            h_ref.detach()
+            rel = lambda a, b: float(np.linalg.norm(a - b) / np.linalg.norm(b))
+            out["parity"] = {"rel_l2_same_factors_1rhs": rel(y_same, y_ref),
+                             "rel_l2_same_factors_256rhs_max": max(rel(Y_same[:, c], Yp_ref[:, i]) for i, c in enumerate(probe)),
+                             "columns_checked_of_256": int(len(probe)), "tolerance": 1e-12,
+                             "what": "reference-built factors: bfMatMul on the CPU vs bfMatMul after bfCudaMatAttach of the same object"}
+            out["same_config"] = {"n": n, "cpu_bfMatMul_ms": float(np.median(cpu_t)) * 1e3, "gpu_bfMatMul_ms": float(np.median(gpu_t[2:])) * 1e3,
+                                  "gpu_bfMatMul_256rhs_ms": t256 * 1e3,
+                                  "api": "bfMatMul through the swapped vtable: malloc'ed result, pageable operand, H2D + D2H inside"}
+            out["same_config"]["speedup"] = out["same_config"]["cpu_bfMatMul_ms"] / out["same_config"]["gpu_bfMatMul_ms"]
         if "--no-dense" not in sys.argv:
             Kx = h_ref.dense_kernel() @ x
             out["reference_vs_dense"] = float(np.linalg.norm(y_ref[:, 0] - Kx) / np.linalg.norm(Kx))

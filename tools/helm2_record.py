@@ -26,7 +26,7 @@ def main():
 
     from butterfly_b200 import capi, helm2
 
-    rec_lib = C.CDLL(str(helm2.HELM2_LIB_PATH), mode=C.RTLD_GLOBAL)  # first: its two builders win
+    rec_lib = helm2.load_recorder()  # first: its two builders win
     from oracle import reflib
 
     att = reflib.load_attach()

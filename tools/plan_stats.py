@@ -5,7 +5,8 @@ from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent / "tests"))
 import numpy as np
-from butterfly_b200 import capi, synth, workloads
+from butterfly_b200 import capi, synth
+from tools import workloads
 from table_interp import Tables
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536

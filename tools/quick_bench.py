@@ -10,7 +10,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 nrhs_list = [int(a) for a in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 256]
 t0 = time.time()
 if len(sys.argv) > 3 and sys.argv[3] == "helm2":
-    from butterfly_b200 import workloads
+    from tools import workloads
     raw, _ = workloads.helm2_circle(n)
 else:
     raw = synth.random_hodbf(n=n, dtype=capi.COMPLEX_F64, seed=1, leaf=64, rank_lo=16, rank_hi=40, with_values=False, exotic=False)

@@ -1,5 +1,6 @@
-"""Benchmark workloads: flattened operators of the named sizes (structure only; values are filled
-on the device by bfCudaPlanFillSynthetic).  Input generation, not part of the apply path."""
+"""Benchmark workloads: flattened operators of the named sizes.  Input generation for bench.py and the
+tools — NOT part of the product package: the generators run the reference's own layout code through the
+oracle build (oracle/_ref), which only the bench and the tests may touch."""
 from __future__ import annotations
 
 import os
@@ -10,8 +11,8 @@ from pathlib import Path
 
 import numpy as np
 
-from . import capi, synth
-from .rawops import RawOps
+from butterfly_b200 import capi, synth
+from butterfly_b200.rawops import RawOps
 
 ROOT = Path(__file__).resolve().parent.parent
 STUB = ROOT / "oracle" / "_ref" / "libbf_shape_stub.so"
@@ -49,7 +50,7 @@ def helm2_circle_recorded(n: int, k: float | None = None, cache_dir: str | None 
     """The same operator laid out INSIDE a recording (tools/helm2_record.py, csrc/bf_helm2_record.c): the
     structure plus the recipes bfCudaPlanBuildHelm2 needs to compute the REAL Helmholtz values on the GPU.
     Returns (RawOps, meta, helm2.Recording); raises if the recorder or the reference build is absent."""
-    from . import helm2
+    from butterfly_b200 import helm2
 
     k = float(k) if k else n / 40.96
     if not (STUB.parent / "libbutterfly_ref.so").exists() or not helm2.HELM2_LIB_PATH.exists():
