@@ -19,6 +19,7 @@
  */
 #define _GNU_SOURCE
 #include <dlfcn.h>
+#include <link.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -138,13 +139,39 @@ static BfCudaHelm2Recipe *newRecipe(struct BfCudaHelm2Recording *r, BfHelm2 cons
   return c;
 }
 
+/* The reference's own definition of `name`: the next one after ours in the search order.  For a library
+ * on the program's link line (`-lbfcuda_helm2 -lbutterfly`) that is dlsym(RTLD_NEXT).  A library brought
+ * in by dlopen (the Python tools) has only its own dependencies in that order — and this one depends on no
+ * libbutterfly on purpose — so as a second step every loaded object is asked for a definition that is not
+ * ours. */
+struct FindNext { const char *name; void *self, *found; };
+static int findNextCb(struct dl_phdr_info *info, size_t size, void *data) {
+  (void)size;
+  struct FindNext *f = data;
+  if (f->found || !info->dlpi_name || !info->dlpi_name[0]) return 0;
+  void *h = dlopen(info->dlpi_name, RTLD_LAZY | RTLD_NOLOAD);
+  if (!h) return 0;
+  void *sym = dlsym(h, f->name);
+  dlclose(h);
+  if (sym && sym != f->self) f->found = sym;
+  return 0;
+}
+static void *forwardTarget(const char *name, void *self) {
+  void *sym = dlsym(RTLD_NEXT, name);
+  if (sym && sym != self) return sym;
+  struct FindNext f = {name, self, NULL};
+  dl_iterate_phdr(findNextCb, &f);
+  return f.found;
+}
+
 BfMat *bfHelm2GetKernelMatrix(BfHelm2 const *helm, BfPoints2 const *Xsrc, BfPoints2 const *Xtgt,
                               BfVectors2 const *Nsrc, BfVectors2 const *Ntgt) {
   struct BfCudaHelm2Recording *r = g_rec;
   if (!r) {
     static KernelFn next;
-    if (!next) next = (KernelFn)dlsym(RTLD_NEXT, "bfHelm2GetKernelMatrix");
-    return next ? next(helm, Xsrc, Xtgt, Nsrc, Ntgt) : NULL;
+    if (!next) next = (KernelFn)forwardTarget("bfHelm2GetKernelMatrix", (void *)bfHelm2GetKernelMatrix);
+    if (!next) { bfSetError(BF_ERROR_RUNTIME_ERROR); return NULL; } /* no libbutterfly loaded behind us */
+    return next(helm, Xsrc, Xtgt, Nsrc, Ntgt);
   }
   /* the argument checks of src/helm2.c:291-295 */
   if ((Nsrc && Nsrc->size != Xsrc->size) || (Ntgt && Ntgt->size != Xtgt->size)) {
@@ -168,8 +195,9 @@ BfMat *bfHelm2GetReexpansionMatrix(BfHelm2 const *helm, BfPoints2 const *srcPtsO
   struct BfCudaHelm2Recording *r = g_rec;
   if (!r) {
     static ReexpFn next;
-    if (!next) next = (ReexpFn)dlsym(RTLD_NEXT, "bfHelm2GetReexpansionMatrix");
-    return next ? next(helm, srcPtsOrig, srcPtsEquiv, srcNormalsOrig, srcNormalsEquiv, tgtPts) : NULL;
+    if (!next) next = (ReexpFn)forwardTarget("bfHelm2GetReexpansionMatrix", (void *)bfHelm2GetReexpansionMatrix);
+    if (!next) { bfSetError(BF_ERROR_RUNTIME_ERROR); return NULL; }
+    return next(helm, srcPtsOrig, srcPtsEquiv, srcNormalsOrig, srcNormalsEquiv, tgtPts);
   }
   /* the argument checks of src/helm2.c:331-342 */
   if ((srcNormalsOrig && srcNormalsOrig->size != srcPtsOrig->size) ||

@@ -137,3 +137,22 @@ def test_recipes_follow_the_leaves_through_sharding_cuts(recorded):
     assert np.array_equal(r2.op_recipe, rec.op_recipe[idx2]) and np.array_equal(r2.op_row_offset, off2)
     rows = rec.recipes["rows"][r2.op_recipe]
     assert (r2.op_row_offset + cut2.ops["m"] <= rows).all()
+
+
+def test_recorder_forwards_outside_a_recording():
+    """Outside a recording the two builders defined by libbfcuda_helm2.so hand the call to the reference's own
+    definitions (csrc/bf_helm2_record.c: forwardTarget).  The library is linked against no libbutterfly, so
+    when it comes in through dlopen the target is found among the loaded objects: an operator built THROUGH
+    the recorder must be bit-identical to the golden output of the plain reference."""
+    _need()
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from butterfly_b200 import helm2; helm2.load_recorder()\n"
+        "from oracle import reflib\n"
+        "h = reflib.Helm2(reflib.circle_points(2048), 50.0)\n"
+        "y, _ = h.matmul(reflib.randn_complex(2048, 0))\n"
+        "m = np.load(%r)\n"
+        "assert np.array_equal(y[:, 0], m['y']), 'forwarded build differs from the reference build'\n"
+    ) % (str(ROOT), str(ROOT / "tests" / "golden" / "helm2_n2048_meta.npz"))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-2000:]
