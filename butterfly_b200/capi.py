@@ -136,13 +136,27 @@ class DebugTables(C.Structure):
         ("wsArena0Rows", C.c_int64),
         ("wsArena1Rows", C.c_int64),
         ("owner", C.c_void_p),
+        ("fusedEnabled", C.c_int32),
+        ("fusedNumCounters", C.c_uint32),
+        ("fusedWsRows", C.c_int64),
+        ("fusedNumItems", C.c_int64),
+        ("fusedNumTiles", C.c_int64),
+        ("fusedItems", C.c_void_p),
+        ("fusedItemDeps", C.c_void_p),
+        ("fusedTiles", C.c_void_p),
+        ("fusedTileDeps", C.c_void_p),
+        ("fusedQItemBegin", C.POINTER(C.c_uint32)),
+        ("fusedQTileBegin", C.POINTER(C.c_uint32)),
     ]
 
 
 ITEM_DTYPE = np.dtype([("outAddr", "<u4"), ("tileBegin", "<u4"), ("rows", "<u2"), ("flags", "<u2"), ("numTiles", "<u4")])
 TILE_DTYPE = np.dtype([("inAddr", "<u4"), ("kc", "<u2"), ("rows", "<u2")])
-KC_IDENTITY, KC_DIAG = 0xFFFF, 0xFFFE
-ITEM_ACCUMULATE = 1
+KC_IDENTITY, KC_DIAG, KC_JUMP = 0xFFFF, 0xFFFE, 0xFFFD
+ITEM_ACCUMULATE, ITEM_JUMP = 1, 2
+NO_COUNTER = 0xFFFFFFFF
+ITEM_DEP_DTYPE = np.dtype([("sig", "<u4"), ("waitTarget", "<u4")])
+TILE_DEP_DTYPE = np.dtype([("idx", "<u4"), ("total", "<u4")])
 SPACE_X, SPACE_Y, SPACE_W = 0, 1, 2
 ROW_MASK = (1 << 30) - 1
 
@@ -161,6 +175,8 @@ EXPORTED_SYMBOLS = [
     "bfCudaMeasureFp64Peak",
     "bfCudaMeasureFp64PeakSustained",
     "bfCudaPlanGetStream",
+    "bfCudaPlanSetFused",
+    "bfCudaPlanGetFused",
     "bfCudaApplyStages",
     "bfCudaPlanGetWorkspace",
     "bfCudaPlanGetWorkspaceLayout",
@@ -278,6 +294,10 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaPlanGetWorkspace.restype = i32
     lib.bfCudaPlanGetWorkspaceLayout.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     lib.bfCudaPlanGetWorkspaceLayout.restype = i32
+    lib.bfCudaPlanSetFused.argtypes = [vp, i32]
+    lib.bfCudaPlanSetFused.restype = i32
+    lib.bfCudaPlanGetFused.argtypes = [vp, i32]
+    lib.bfCudaPlanGetFused.restype = i32
     lib.bfCudaPlanGetStream.argtypes = [vp]
     lib.bfCudaPlanGetStream.restype = vp
     lib.bfCudaSolveGMRES.argtypes = [vp, vp, vp, C.c_double, i64, vp, C.POINTER(i64), C.POINTER(C.c_double), C.POINTER(i64)]

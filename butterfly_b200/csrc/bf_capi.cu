@@ -70,6 +70,30 @@ static BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
   } else {
     BF_CUDA_TRY(cudaMemset(dd.pool, 0, poolBytes));
   }
+  // fused single-launch tables (1-RHS apply): uploaded once, host copies dropped
+  FusedTables &F = D.fused;
+  if (F.enabled) {
+    auto up = [&](auto **dst, const auto &vec) -> cudaError_t {
+      using V = typename std::remove_reference<decltype(vec)>::type::value_type;
+      cudaError_t e = cudaMalloc(dst, std::max<size_t>(vec.size(), 1) * sizeof(V));
+      if (e == cudaSuccess && !vec.empty()) e = cudaMemcpy(*dst, vec.data(), vec.size() * sizeof(V), cudaMemcpyHostToDevice);
+      return e;
+    };
+    BF_CUDA_TRY(up(&dd.fItems, F.items));
+    BF_CUDA_TRY(up(&dd.fItemDeps, F.itemDeps));
+    BF_CUDA_TRY(up(&dd.fTiles, F.tiles));
+    BF_CUDA_TRY(up(&dd.fTileDeps, F.tileDeps));
+    BF_CUDA_TRY(up(&dd.fqItemBegin, F.qItemBegin));
+    BF_CUDA_TRY(up(&dd.fqTileBegin, F.qTileBegin));
+    dd.numCounters = F.numCounters;
+    BF_CUDA_TRY(cudaMalloc(&dd.counters, std::max<size_t>(2 * (size_t)F.numCounters, 1) * sizeof(uint32_t)));
+    BF_CUDA_TRY(cudaMemset(dd.counters, 0, std::max<size_t>(2 * (size_t)F.numCounters, 1) * sizeof(uint32_t)));
+    dd.fusedWsRows = F.wsRows;
+    dd.tableBytes += (int64_t)(F.items.size() * 24 + F.tiles.size() * 16 + 2 * (Q + 1) * 4 + 2 * (size_t)F.numCounters * 4);
+    dd.fusedReady = true;
+    F.items = {}; F.itemDeps = {}; F.tiles = {}; F.tileDeps = {}; // device-resident now
+  }
+  (void)P;
   dd.built = true;
   return BF_CUDA_OK;
 }
@@ -134,6 +158,8 @@ BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **out) {
   std::unique_ptr<BfCudaPlan> P(new BfCudaPlan());
   P->device = dev;
   P->numSMs = prop.multiProcessorCount;
+  P->cooperativeOk = prop.cooperativeLaunch != 0;
+  if (const char *e = std::getenv("BF_CUDA_FUSED")) P->fusedEnabled = std::atoi(e) != 0;
   P->dtype = desc->dtype;
   P->numRows = desc->numRows;
   P->numCols = desc->numCols;
@@ -206,6 +232,15 @@ BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *P, int32_t enable) {
   return BF_CUDA_OK;
 }
 
+BfCudaStatus bfCudaPlanSetFused(BfCudaPlan *P, int32_t enable) {
+  if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  P->fusedEnabled = enable != 0;
+  return BF_CUDA_OK;
+}
+int32_t bfCudaPlanGetFused(const BfCudaPlan *P, int32_t op) {
+  return P && op >= 0 && op <= 2 && P->dir[op].built && P->dir[op].fusedReady && P->cooperativeOk && P->fusedEnabled && !P->profiling;
+}
+
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *P) { return P ? P->lastLaunches : 0; }
 void *bfCudaPlanGetStream(const BfCudaPlan *P) { return P ? (void *)P->stream : nullptr; }
 
@@ -261,8 +296,10 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
   const int32_t *scatterIn = op == BF_CUDA_OP_N ? P->inPerm : P->invOutPerm;
   const int32_t *scatterOut = op == BF_CUDA_OP_N ? P->outPerm : P->invInPerm;
 
+  // 1 RHS, whole apply: ONE cooperative launch over the fused tables (flat workspace, readiness counters)
+  const bool fused = nrhs == 1 && dd.fusedReady && P->cooperativeOk && P->fusedEnabled && !P->profiling && !staged;
   // column chunking keeps the workspace within budget
-  const size_t rowsPad = (size_t)D.wsRows + 2;
+  const size_t rowsPad = (size_t)(fused ? std::max(D.wsRows, dd.fusedWsRows) : D.wsRows) + 2;
   const size_t xRowsPad = (size_t)D.rowsIn + 2;
   int64_t chunk = nrhs;
   while (chunk > 1 && (rowsPad + xRowsPad) * (size_t)chunk * es > P->maxScratchBytes) chunk = (chunk + 1) / 2;
@@ -308,6 +345,25 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
       a.base[kSpaceX] = xs; a.ld[kSpaceX] = nc;
     } else {
       a.base[kSpaceX] = const_cast<unsigned char *>(xp); a.ld[kSpaceX] = ldx;
+    }
+    if (fused) {
+      a.pdl = 0;
+      a.items = dd.fItems; a.tiles = dd.fTiles;
+      a.itemDeps = dd.fItemDeps; a.tileDeps = dd.fTileDeps;
+      a.qItemBegin = dd.fqItemBegin; a.qTileBegin = dd.fqTileBegin; a.qPool16 = nullptr;
+      a.numCounters = dd.numCounters;
+      a.cnt = dd.counters + (size_t)(dd.applyParity & 1u) * dd.numCounters;
+      a.cntNext = dd.counters + (size_t)((dd.applyParity & 1u) ^ 1u) * dd.numCounters;
+      cudaError_t e = launchGemvFused(P->dtype, a, stream);
+      if (e == cudaErrorCooperativeLaunchTooLarge) { // the CTAs cannot all be resident: per-stage launches from now on
+        cudaGetLastError();
+        P->cooperativeOk = false;
+        return applyImpl(P, op, d_x, ldx, nrhs, d_y, ldy, streamOpaque, sBegin, sEnd, staged);
+      }
+      if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("fused apply launch: ") + cudaGetErrorString(e));
+      ++dd.applyParity;
+      ++launches;
+      continue;
     }
     for (size_t s = (size_t)sBegin; s < (size_t)sEnd; ++s) {
       if (P->profiling && c0 == 0) BF_CUDA_TRY(cudaEventRecord(P->events[s], stream));

@@ -69,6 +69,14 @@ extern "C" BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t o
   t.pool16 = D.pool16; t.pool = anyVal ? o->pool.data() : nullptr;
   t.wsArena0Rows = D.wsArena[0]; t.wsArena1Rows = D.wsArena[1];
   t.owner = o;
+  const FusedTables &F = D.fused;
+  t.fusedEnabled = F.enabled ? 1 : 0;
+  t.fusedNumCounters = F.numCounters;
+  t.fusedWsRows = F.wsRows;
+  t.fusedNumItems = (int64_t)F.items.size(); t.fusedNumTiles = (int64_t)F.tiles.size();
+  t.fusedItems = F.items.data(); t.fusedItemDeps = F.itemDeps.data();
+  t.fusedTiles = F.tiles.data(); t.fusedTileDeps = F.tileDeps.data();
+  t.fusedQItemBegin = F.qItemBegin.data(); t.fusedQTileBegin = F.qTileBegin.data();
   *out = &t;
   return BF_CUDA_OK;
 }

@@ -48,10 +48,25 @@ struct DevDirection {
   unsigned char *pool = nullptr;
   std::vector<size_t> itemOff, tileOff; // per stage
   int64_t tableBytes = 0;
+  // fused single-launch tables (FusedTables) and the two alternating counter sets
+  bool fusedReady = false;
+  DevItem *fItems = nullptr;
+  DevTile *fTiles = nullptr;
+  ItemDep *fItemDeps = nullptr;
+  TileDep *fTileDeps = nullptr;
+  uint32_t *fqItemBegin = nullptr, *fqTileBegin = nullptr;
+  uint32_t *counters = nullptr; // [2][numCounters]
+  uint32_t numCounters = 0;
+  int64_t fusedWsRows = 0;
+  unsigned applyParity = 0;
   void release() {
     cudaFree(items); cudaFree(tiles); cudaFree(qItemBegin); cudaFree(qTileBegin); cudaFree(qPool16); cudaFree(pool);
+    cudaFree(fItems); cudaFree(fTiles); cudaFree(fItemDeps); cudaFree(fTileDeps); cudaFree(fqItemBegin); cudaFree(fqTileBegin);
+    cudaFree(counters);
     items = nullptr; tiles = nullptr; qItemBegin = qTileBegin = nullptr; qPool16 = nullptr; pool = nullptr;
-    built = false;
+    fItems = nullptr; fTiles = nullptr; fItemDeps = nullptr; fTileDeps = nullptr; fqItemBegin = fqTileBegin = nullptr;
+    counters = nullptr;
+    built = false; fusedReady = false;
   }
 };
 } // namespace bfc
@@ -81,5 +96,7 @@ struct BfCudaPlan {
   std::vector<cudaEvent_t> events;
   int64_t lastStages = 0;
   size_t maxScratchBytes = size_t(24) << 30;
+  bool cooperativeOk = false; // device supports cooperative launches (the fused 1-RHS apply needs co-resident CTAs)
+  bool fusedEnabled = true;   // bfCudaPlanSetFused / BF_CUDA_FUSED=0: per-stage launches only (A/B measurements)
 };
 

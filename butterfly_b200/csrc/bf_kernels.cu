@@ -55,6 +55,12 @@ __device__ __forceinline__ void bulkLoadHint(uint32_t dst, const void *src, uint
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
 }
+__device__ __forceinline__ void fenceProxyAsyncGlobal() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ uint32_t loadAcquire(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void fenceBarrierInit() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void fenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -129,7 +135,16 @@ __device__ __forceinline__ void tileFma(typename Scalar<CPLX>::T (&acc)[P], cons
 }
 
 // ---- 1-RHS stage kernel ---------------------------------------------------------------------------
-template <bool CPLX>
+//
+// FUSED = the whole apply in ONE launch (bf_plan.hpp, FusedTables): the tables are queue-major over all
+// stages, a warp never leaves its ring, and the grid-wide barrier between stages is replaced by readiness
+// counters — lane 0 checks (ld.acquire) that every writer of a tile's operand buffer has signalled before it
+// issues the tile's bulk copies; an item signals (fence + atomic add) after its store.  A tile whose operand is
+// not ready yet is simply not staged (the warp goes on consuming what it has) unless the consumer has nothing
+// else to do, in which case it spins: all CTAs are co-resident (cooperative launch, one CTA per SM) and every
+// wait is on items of an EARLIER stage, which a warp reaches without waiting on anything of this one, so the
+// spin always ends.  The counters of the NEXT apply are zeroed here (two sets, alternating).
+template <bool CPLX, bool FUSED>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid_constant__ StageLaunch a) {
   using S = Scalar<CPLX>;
   using T = typename S::T;
@@ -163,6 +178,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     }
   };
   const int q = blockIdx.x * kWarpsPerCta + warp;
+  if (FUSED) { // zero the counter set of the next apply (the previous user of that set has completed: stream order)
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.numCounters; i += gridDim.x * blockDim.x) a.cntNext[i] = 0u;
+  }
   if (q >= a.numQueues) { pdlSync(); return; }
   const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
   const uint32_t tBeg = a.qTileBegin[q], tEnd = a.qTileBegin[q + 1];
@@ -176,9 +194,16 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   const uint4 *itemTab = reinterpret_cast<const uint4 *>(a.items);
   auto loadTiles = [&](uint32_t base) -> uint64_t { return base + lane < tEnd ? tileTab[base + lane] : 0ull; };
   auto loadItems = [&](uint32_t base) -> uint4 { return base + lane < iEnd ? itemTab[base + lane] : make_uint4(0u, 0u, 0u, 0u); };
+  // fused tables: the dependency words travel in windows of their own, slid together with the descriptors
+  const uint64_t *tileDepTab = reinterpret_cast<const uint64_t *>(a.tileDeps);
+  const uint64_t *itemDepTab = reinterpret_cast<const uint64_t *>(a.itemDeps);
+  auto loadTileDeps = [&](uint32_t base) -> uint64_t { return (FUSED && base + lane < tEnd) ? tileDepTab[base + lane] : ~0ull; };
+  auto loadItemDeps = [&](uint32_t base) -> uint64_t { return (FUSED && base + lane < iEnd) ? itemDepTab[base + lane] : ~0ull; };
   uint32_t twBase = tBeg, iwBase = iBeg;
   uint64_t tw0 = loadTiles(twBase), tw1 = loadTiles(twBase + 32);
   uint4 iw0 = loadItems(iwBase), iw1 = loadItems(iwBase + 32);
+  uint64_t td0 = loadTileDeps(twBase), td1 = loadTileDeps(twBase + 32);
+  uint64_t id0 = loadItemDeps(iwBase), id1 = loadItemDeps(iwBase + 32);
   auto getTile = [&](uint32_t t) -> DevTile {
     const uint32_t off = t - twBase; // warp-uniform
     uint64_t v;
@@ -189,9 +214,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     d.inAddr = (uint32_t)v; d.kc = (uint16_t)(v >> 32); d.rows = (uint16_t)(v >> 48);
     return d;
   };
+  auto getTileDep = [&](uint32_t t) -> uint64_t { // low word: counter, high word: its final value
+    const uint32_t off = t - twBase;
+    if (off < 32) return __shfl_sync(0xffffffffu, td0, off);
+    if (off < 64) return __shfl_sync(0xffffffffu, td1, off - 32);
+    return tileDepTab[t];
+  };
+  uint64_t curItemDep = ~0ull;
   auto getItem = [&](uint32_t i) -> DevItem {
-    if (i - iwBase >= 32) { iw0 = iw1; iwBase += 32; iw1 = loadItems(iwBase + 32); }
+    if (i - iwBase >= 32) {
+      iw0 = iw1; iwBase += 32; iw1 = loadItems(iwBase + 32);
+      if (FUSED) { id0 = id1; id1 = loadItemDeps(iwBase + 32); }
+    }
     const uint32_t off = i - iwBase;
+    if (FUSED) curItemDep = __shfl_sync(0xffffffffu, id0, off);
     DevItem d;
     d.outAddr = __shfl_sync(0xffffffffu, iw0.x, off);
     d.tileBegin = __shfl_sync(0xffffffffu, iw0.y, off);
@@ -212,14 +248,38 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   auto inRowPtr = [&](uint32_t addr) -> const unsigned char * {
     return ((addr >> 30) == kSpaceX ? baseX : baseW) + (size_t)(addr & kRowMask) * ES;
   };
-  auto produce = [&]() {
+  // readiness counters (FUSED): spin = wait until counter `idx` has reached `target`; otherwise one look
+  uint32_t readyIdx = kNoCounter; // the last operand-buffer counter seen complete (tiles of an item mostly share it)
+  auto counterReached = [&](uint32_t idx, uint32_t target, bool spin) -> bool {
+    uint32_t v = 0;
+    if (lane == 0) {
+      v = loadAcquire(a.cnt + idx);
+      while (spin && v < target) { __nanosleep(40); v = loadAcquire(a.cnt + idx); }
+    }
+    v = __shfl_sync(0xffffffffu, v, 0);
+    return v >= target;
+  };
+  // Stage the next tile of the queue.  Returns false when there is none left, or (FUSED, !block) when its
+  // operand is not complete yet — the cursor then stays on it.
+  auto produce = [&](bool block) -> bool {
     while (pT < tEnd) {
       const DevTile t = getTile(pT);
-      ++pT;
-      if (t.kc >= kKcDiag) { // identity / diagonal tiles are read directly by the consumer
-        pPool += tileBytes(ES, t.rows, t.kc);
+      if (t.kc >= kKcJump) { // identity / diagonal tiles are read directly by the consumer; jumps move the cursor
+        if (t.kc == kKcJump) pPool = a.pool + (((unsigned long long)t.rows << 32) | t.inAddr) * 16ull;
+        else pPool += tileBytes(ES, t.rows, t.kc);
+        ++pT;
         continue;
       }
+      if (FUSED) {
+        const uint64_t dep = getTileDep(pT);
+        const uint32_t idx = (uint32_t)dep;
+        if (idx != kNoCounter && idx != readyIdx) {
+          if (!counterReached(idx, (uint32_t)(dep >> 32), block)) return false;
+          readyIdx = idx;
+          if (lane == 0) fenceProxyAsyncGlobal(); // generic-proxy stores of other SMs -> this thread's bulk copies
+        }
+      }
+      ++pT;
       const uint32_t bytes = CPLX ? (uint32_t)t.rows * t.kc * 16u : ((uint32_t)t.rows * t.kc * 8u + 15u) & ~15u;
       const unsigned char *src = pPool;
       pPool += bytes;
@@ -241,8 +301,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
         bulkLoad(dst + kTileBytes, xsrc, xb, bar);
       }
       ++pSeq;
-      return;
+      return true;
     }
+    return false;
   };
   // Programmatic dependent launch (small operators only, bf_capi.cu): everything above (barriers, queue
   // bounds, descriptor windows — static plan tables) may overlap the tail of the previous stage; its results
@@ -252,7 +313,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   // 10.67 -> 10.85 ms at N = 524 288 — hence the size switch.
   pdlSync();
 #pragma unroll 1
-  for (int s = 0; s < kGemvSlots; ++s) produce();
+  for (int s = 0; s < kGemvSlots; ++s)
+    if (!produce(false)) break;
 
   const int g = lane / G, l = lane % G;
 #pragma unroll 1
@@ -269,16 +331,34 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
 
 #pragma unroll 1
     for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) {
-      if (t - twBase >= 32 && pT - twBase >= 32) { tw0 = tw1; twBase += 32; tw1 = loadTiles(twBase + 32); } // both cursors left window 0
+      if (t - twBase >= 32 && pT - twBase >= 32) { // both cursors left window 0
+        tw0 = tw1; twBase += 32; tw1 = loadTiles(twBase + 32);
+        if (FUSED) { td0 = td1; td1 = loadTileDeps(twBase + 32); }
+      }
       const DevTile tl = getTile(t);
-      if (tl.kc >= kKcDiag) {
+      if (tl.kc >= kKcJump) {
+        if (tl.kc == kKcJump) {
+          cPool = a.pool + (((unsigned long long)tl.rows << 32) | tl.inAddr) * 16ull;
+          continue;
+        }
+        if (FUSED) { // read with plain loads: wait for the operand here (L1 is bypassed: other SMs wrote it)
+          const uint64_t dep = getTileDep(t);
+          if ((uint32_t)dep != kNoCounter && (uint32_t)dep != readyIdx) {
+            counterReached((uint32_t)dep, (uint32_t)(dep >> 32), true);
+            readyIdx = (uint32_t)dep;
+          }
+        }
         if (lane < rows) {
-          const T xv = *reinterpret_cast<const T *>(inRowPtr(tl.inAddr) + (size_t)lane * ES);
+          const T *xp = reinterpret_cast<const T *>(inRowPtr(tl.inAddr) + (size_t)lane * ES);
+          const T xv = FUSED ? __ldcg(xp) : *xp;
           const double d = tl.kc == kKcDiag ? reinterpret_cast<const double *>(cPool)[lane] : 1.0;
           S::fmaReal(extra, d, xv);
         }
         cPool += tileBytes(ES, tl.rows, tl.kc);
         continue;
+      }
+      if (FUSED) { // the tile must have been staged: now the consumer has nothing else to do, so spin if need be
+        while (pSeq == cSeq) produce(true);
       }
       const int kc = tl.kc;
       const uint32_t bytes = CPLX ? (uint32_t)rows * kc * 16u : ((uint32_t)rows * kc * 8u + 15u) & ~15u;
@@ -302,10 +382,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       default: tileFma<CPLX, 8, P, RPP, G>(acc, A, xs, rp, rows, kc, l); break;
       }
       __syncwarp();
-      produce(); // refill the slot just drained
       ++cSeq;
       cPool += bytes;
+      if (FUSED) { // refill what is free; a tile whose operand is not complete yet stays where it is
+        while (pSeq - cSeq < (uint32_t)kGemvSlots && produce(false)) {}
+      } else {
+        produce(false); // refill the slot just drained
+      }
     }
+    if (FUSED && (it.flags & kItemJump)) continue; // pseudo item: nothing to reduce or store
 
     // One reduction per item over the G lanes of a row, then row r -> lane r for a coalesced store.  The 8
     // passes are shared out over the lanes as the butterfly halves (lane l keeps the passes whose bit matches
@@ -333,13 +418,23 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     // (r % RPP) * G + r / RPP
     T out = S::shfl(mine, (lane % RPP) * G + lane / RPP);
     out = S::add(out, extra);
+    if (FUSED && (it.flags & kItemAccumulate) && (uint32_t)curItemDep != kNoCounter)
+      counterReached((uint32_t)curItemDep, (uint32_t)(curItemDep >> 32), true); // the earlier stages' share of these rows
     if (lane < rows) {
       const uint32_t sp = it.outAddr >> 30;
       long long row = (long long)(it.outAddr & kRowMask) + lane;
       if (sp == kSpaceY && a.outPerm) row = a.outPerm[row];
       T *dst = reinterpret_cast<T *>(a.base[sp] + row * a.ld[sp] * ES);
-      if (it.flags & kItemAccumulate) out = S::add(out, *dst);
+      if (it.flags & kItemAccumulate) out = S::add(out, FUSED ? __ldcg(dst) : *dst);
       *dst = out;
+    }
+    if (FUSED && (uint32_t)curItemDep != kNoCounter) { // signal: the rows are complete as far as this stage goes
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        fenceProxyAsyncGlobal();
+        atomicAdd(a.cnt + (uint32_t)curItemDep, 1u);
+      }
     }
   }
 }
@@ -816,9 +911,13 @@ cudaError_t launchFillSynthetic(int dtype, unsigned char *pool, const FillPiece 
 // ---- launchers ----------------------------------------------------------------------------------------
 cudaError_t configureKernels() {
   cudaError_t e;
-  e = cudaFuncSetAttribute(bfGemvStage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(bfGemvStage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfGemvStage<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfGemvStage<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(bfWideMmaStage<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaSmemBytes);
   if (e != cudaSuccess) return e;
@@ -840,7 +939,24 @@ cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int /*numSMs*/, cud
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = a.pdl ? 1 : 0;
-  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false>, a);
+  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, false>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, false>, a);
+}
+
+// The whole 1-RHS apply as one cooperative launch (all CTAs co-resident: the readiness spins rely on it).
+cudaError_t launchGemvFused(int dtype, const StageLaunch &a, cudaStream_t stream) {
+  const int ctas = (a.numQueues + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (ctas == 0) return cudaSuccess;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas);
+  cfg.blockDim = dim3(kWarpsPerCta * 32);
+  cfg.dynamicSmemBytes = kGemvSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, true>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, true>, a);
 }
 
 template <bool CPLX, int CT>

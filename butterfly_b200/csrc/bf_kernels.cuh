@@ -23,6 +23,12 @@ struct StageLaunch {
   int nrhs;
   int colBegin;               // first RHS column this launch handles (wide kernel)
   int pdl;                    // 1-RHS kernel: launched with programmatic stream serialization (small operators)
+  // fused single-launch apply (FusedTables): dependency words parallel to items / tiles, the counter set of
+  // this apply and the one to zero for the next
+  const ItemDep *itemDeps;
+  const TileDep *tileDeps;
+  uint32_t *cnt, *cntNext;
+  uint32_t numCounters;
 };
 
 // Shared-memory geometry of the 1-RHS kernel (one ring of kGemvSlots slots per warp).
@@ -44,6 +50,8 @@ constexpr int kMmaSmemBytes = kMmaRingBytes + kMmaBars * (8 + 8 + 16) + 64;
 
 // 1 RHS: y = A x, one warp per queue, TMA-staged tiles, shuffle reductions.
 cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);
+// 1 RHS, all stages in one cooperative launch (`a` carries the fused tables and the counters).
+cudaError_t launchGemvFused(int dtype, const StageLaunch &a, cudaStream_t stream);
 // nrhs >= 2: one CTA per kWarpsPerCta queues, columns across threads.
 cudaError_t launchWideStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);
 cudaError_t configureKernels(); // opt in to the large dynamic shared memory carve-outs

@@ -37,6 +37,129 @@ struct Elem {
 };
 } // namespace
 
+static void buildFused(const BfCudaPlanDesc &desc, Direction &D, const std::vector<int32_t> &firstW,
+                       const std::vector<int32_t> &lastW) {
+  FusedTables &F = D.fused;
+  F = FusedTables();
+  for (const DirOp &d : D.ops)
+    if (d.remote) return; // block-row shards exchange rows between stages: per-stage launches
+  const int64_t nB = desc.numBufs;
+  const int nQ = D.numQueues;
+  const size_t nS = D.stages.size();
+  // flat workspace: every written temp gets rows of its own (even count keeps real rows 16-byte aligned)
+  std::vector<int64_t> flatOff((size_t)nB, -1);
+  int64_t flatRows = 0;
+  for (int64_t b = 0; b < nB; ++b) {
+    if (b == D.inBufId || b == D.outBufId || lastW[(size_t)b] < 0) continue;
+    flatOff[(size_t)b] = flatRows;
+    flatRows += (desc.bufRows[b] + 1) & ~int64_t(1);
+  }
+  if (flatRows > (int64_t)kRowMask) return; // does not fit the 30-bit row addresses: keep per-stage launches
+  F.wsRows = flatRows;
+  (void)firstW;
+  // counters.  Workspace buffer: one per buffer, bumped by every item that writes it.  Result (Y): one per
+  // elementary interval that more than one stage writes (near-field rows + butterflies of different depth
+  // accumulating into the same MatBlockDense row block); other result rows need none.
+  std::vector<uint32_t> bufCounter((size_t)nB, kNoCounter), bufTotal((size_t)nB, 0);
+  uint32_t nC = 0;
+  for (int64_t b = 0; b < nB; ++b)
+    if (flatOff[(size_t)b] >= 0) bufCounter[(size_t)b] = nC++;
+  int64_t numElems = 0;
+  for (const Stage &S : D.stages)
+    for (int64_t e : S.itemElem) numElems = std::max(numElems, e + 1);
+  std::vector<int32_t> elemFirstStage((size_t)numElems, -1);
+  std::vector<uint8_t> elemMulti((size_t)numElems, 0);
+  for (size_t s = 0; s < nS; ++s) {
+    const Stage &S = D.stages[s];
+    for (size_t i = 0; i < S.items.size(); ++i) {
+      const int64_t b = S.itemBuf[i], e = S.itemElem[i];
+      if (b == D.outBufId) {
+        if (elemFirstStage[(size_t)e] < 0) elemFirstStage[(size_t)e] = (int32_t)s;
+        else if (elemFirstStage[(size_t)e] != (int32_t)s) elemMulti[(size_t)e] = 1;
+      } else {
+        ++bufTotal[(size_t)b];
+      }
+    }
+  }
+  std::vector<uint32_t> elemCounter((size_t)numElems, kNoCounter);
+  for (int64_t e = 0; e < numElems; ++e)
+    if (elemMulti[(size_t)e]) elemCounter[(size_t)e] = nC++;
+  F.numCounters = nC;
+  // signals seen so far per counter, stage by stage: an accumulating item at stage s waits for the signals
+  // of all earlier stages on its counter
+  std::vector<uint32_t> before(nC, 0), during(nC, 0);
+  std::vector<std::vector<ItemDep>> itemDeps(nS);
+  for (size_t s = 0; s < nS; ++s) {
+    const Stage &S = D.stages[s];
+    itemDeps[s].resize(S.items.size());
+    for (size_t i = 0; i < S.items.size(); ++i) {
+      const int64_t b = S.itemBuf[i];
+      const uint32_t c = b == D.outBufId ? elemCounter[(size_t)S.itemElem[i]] : bufCounter[(size_t)b];
+      ItemDep dep{c, 0};
+      if (c != kNoCounter) {
+        if (S.items[i].flags & kItemAccumulate) dep.waitTarget = before[c];
+        ++during[c];
+      }
+      itemDeps[s][i] = dep;
+    }
+    for (size_t i = 0; i < S.items.size(); ++i) {
+      const uint32_t c = itemDeps[s][i].sig;
+      if (c != kNoCounter && during[c]) { before[c] += during[c]; during[c] = 0; }
+    }
+  }
+  auto flatAddr = [&](int64_t buf, int64_t row) -> uint32_t {
+    if (buf == D.inBufId) return packAddr(kSpaceX, row);
+    if (buf == D.outBufId) return packAddr(kSpaceY, row);
+    return packAddr(kSpaceW, flatOff[(size_t)buf] + row);
+  };
+  // queue-major concatenation
+  F.qItemBegin.assign((size_t)nQ + 1, 0);
+  F.qTileBegin.assign((size_t)nQ + 1, 0);
+  size_t totalItems = 0, totalTiles = 0;
+  for (const Stage &S : D.stages) { totalItems += S.items.size(); totalTiles += S.tiles.size(); }
+  F.items.reserve(totalItems + nS * (size_t)nQ / 2);
+  F.itemDeps.reserve(totalItems + nS * (size_t)nQ / 2);
+  F.tiles.reserve(totalTiles + nS * (size_t)nQ / 2);
+  F.tileDeps.reserve(totalTiles + nS * (size_t)nQ / 2);
+  for (int q = 0; q < nQ; ++q) {
+    F.qItemBegin[(size_t)q] = (uint32_t)F.items.size();
+    F.qTileBegin[(size_t)q] = (uint32_t)F.tiles.size();
+    for (size_t s = 0; s < nS; ++s) {
+      const Stage &S = D.stages[s];
+      const uint32_t i0 = S.qItemBegin[(size_t)q], i1 = S.qItemBegin[(size_t)q + 1];
+      if (i0 == i1) continue;
+      { // the queue's pool span of this stage starts here
+        const uint64_t p16 = S.qPool16[(size_t)q];
+        DevItem ji{0u, (uint32_t)F.tiles.size(), 0, kItemJump, 1u};
+        F.items.push_back(ji);
+        F.itemDeps.push_back(ItemDep{kNoCounter, 0});
+        F.tiles.push_back(DevTile{(uint32_t)(p16 & 0xFFFFFFFFull), kKcJump, (uint16_t)(p16 >> 32)});
+        F.tileDeps.push_back(TileDep{kNoCounter, 0});
+      }
+      for (uint32_t i = i0; i < i1; ++i) {
+        DevItem it = S.items[i];
+        const uint32_t tb = it.tileBegin;
+        it.outAddr = flatAddr(S.itemBuf[i], S.itemRow[i]);
+        it.tileBegin = (uint32_t)F.tiles.size();
+        F.items.push_back(it);
+        F.itemDeps.push_back(itemDeps[s][i]);
+        for (uint32_t t = tb; t < tb + it.numTiles; ++t) {
+          DevTile tl = S.tiles[t];
+          const int64_t b = S.tileBuf[t];
+          tl.inAddr = flatAddr(b, S.tileRow[t]);
+          F.tiles.push_back(tl);
+          const uint32_t c = (b == D.inBufId) ? kNoCounter : bufCounter[(size_t)b];
+          F.tileDeps.push_back(TileDep{c, c == kNoCounter ? 0u : bufTotal[(size_t)b]});
+        }
+      }
+    }
+  }
+  F.qItemBegin[(size_t)nQ] = (uint32_t)F.items.size();
+  F.qTileBegin[(size_t)nQ] = (uint32_t)F.tiles.size();
+  if (F.tiles.size() > 0xFFFFFFF0ull || D.pool16 >> 48) { F = FusedTables(); return; }
+  F.enabled = true;
+}
+
 BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQueues, Direction &D,
                               std::string &err) {
   const bool cplx = desc.dtype == BF_CUDA_COMPLEX_F64;
@@ -286,6 +409,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
             DevTile t{addrOf(d.inBuf, d.inOff + rowInOp), d.kind == BF_CUDA_LEAF_DIAG ? kKcDiag : kKcIdentity, (uint16_t)rows};
             S.tiles.push_back(t);
             S.pieces.push_back(PieceRef{frags[q].seq, (int32_t)rowInOp, (int32_t)rowInOp});
+            S.tileBuf.push_back(d.inBuf); S.tileRow.push_back(d.inOff + rowInOp);
             continue;
           }
           const int64_t nK = (d.k + KC - 1) / KC;
@@ -296,6 +420,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
             DevTile t{addrOf(d.inBuf, d.inOff + c0), (uint16_t)(c1 - c0), (uint16_t)rows};
             S.tiles.push_back(t);
             S.pieces.push_back(PieceRef{frags[q].seq, (int32_t)rowInOp, (int32_t)c0});
+            S.tileBuf.push_back(d.inBuf); S.tileRow.push_back(d.inOff + c0);
             D.maxTileK = std::max<int64_t>(D.maxTileK, c1 - c0);
           }
           S.entries += (int64_t)rows * d.k;
@@ -303,6 +428,7 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
       }
       it.numTiles = (uint32_t)S.tiles.size() - it.tileBegin;
       S.items.push_back(it);
+      S.itemBuf.push_back(el.buf); S.itemElem.push_back(frags[f].elem); S.itemRow.push_back(el.start + r0);
       D.maxItemRows = std::max<int64_t>(D.maxItemRows, rows);
     }
     f = f1;
@@ -353,6 +479,9 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     D.numTiles += (int64_t)nT;
   }
   D.pool16 = pool16;
+
+  // ---- 7. fused (single-launch) tables: queue-major, flat workspace, readiness counters ------------
+  buildFused(desc, D, firstW, lastW);
   return BF_CUDA_OK;
 }
 

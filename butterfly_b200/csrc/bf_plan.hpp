@@ -41,7 +41,11 @@ inline uint32_t packAddr(uint32_t space, int64_t row) { return (space << 30) | (
 constexpr uint16_t kKcIdentity = 0xFFFF; // y[r] += x[r]           (no pool bytes)
 constexpr uint16_t kKcDiag = 0xFFFE;     // y[r] += d[r] * x[r]    (pool: rows doubles, padded to 16 B)
 
+constexpr uint16_t kKcJump = 0xFFFD;     // fused tables only: the queue's pool cursor moves to 16 * (rows << 32 | inAddr)
+
 constexpr uint16_t kItemAccumulate = 1;  // rows already hold a partial result from an earlier stage
+constexpr uint16_t kItemJump = 2;        // fused tables only: pseudo item (rows == 0) whose single tile is a kKcJump
+constexpr uint32_t kNoCounter = 0xFFFFFFFFu;
 
 struct DevItem {      // 16 B
   uint32_t outAddr;   // first output row
@@ -56,6 +60,37 @@ struct DevTile {      // 8 B
   uint16_t rows;      // == owning item's rows (lets the prefetcher run ahead of the consumer)
 };
 static_assert(sizeof(DevItem) == 16 && sizeof(DevTile) == 8, "table ABI");
+
+// ---- fused (single-launch) tables ---------------------------------------------------------------
+// The 1-RHS apply can run as ONE persistent kernel: warp q walks the concatenation of its queue over all
+// stages, and the stage barrier is replaced by readiness counters.  The tables are a queue-major copy of
+// the stage-major ones with
+//   * workspace rows in a FLAT layout (every intermediate buffer has rows of its own: nothing is reused
+//     inside an apply, so there are no write-after-read hazards and only true dependencies remain; at one
+//     RHS column the extra rows cost megabytes),
+//   * one counter per written workspace buffer and per result segment that several stages accumulate into;
+//     an item bumps its counter after its store, a tile waits until every writer of its operand buffer has
+//     done so, an accumulating item until the earlier stages' writers have,
+//   * a jump pseudo item / tile wherever the queue's pool span is not contiguous (stage boundaries).
+struct ItemDep {        // 8 B, parallel to the fused items
+  uint32_t sig;         // counter bumped after the store (kNoCounter: nobody waits for these rows)
+  uint32_t waitTarget;  // accumulating items: value the same counter must have reached before the read-modify-write
+};
+struct TileDep {        // 8 B, parallel to the fused tiles
+  uint32_t idx;         // counter of the operand's buffer (kNoCounter: the operand is X)
+  uint32_t total;       // its final value = number of items that write that buffer
+};
+struct FusedTables {
+  bool enabled = false;
+  std::vector<DevItem> items;       // tileBegin indexes `tiles` below
+  std::vector<ItemDep> itemDeps;
+  std::vector<DevTile> tiles;
+  std::vector<TileDep> tileDeps;
+  std::vector<uint32_t> qItemBegin; // [numQueues + 1]
+  std::vector<uint32_t> qTileBegin; // [numQueues + 1]
+  uint32_t numCounters = 0;
+  int64_t wsRows = 0;               // rows of the flat workspace
+};
 
 // Where a tile's values come from (host only; used by packing and by the synthetic fill).
 struct PieceRef {
@@ -86,6 +121,9 @@ struct Stage {
   std::vector<uint32_t> qTileBegin;   // [numQueues + 1]
   std::vector<uint64_t> qPool16;      // [numQueues + 1] pool offset (16-byte units) where a queue starts
   std::vector<uint64_t> tilePool16;   // [numTiles] pool offset of every tile (host only)
+  std::vector<int64_t> itemBuf, itemElem; // per item: buffer written, elementary interval (host only; fused tables)
+  std::vector<int64_t> itemRow;       // per item: first row inside that buffer
+  std::vector<int64_t> tileBuf, tileRow; // per tile: buffer read and first row read (-1 for jump tiles)
   uint64_t poolBegin16 = 0, poolEnd16 = 0;
   int64_t entries = 0;                // dense entries applied in this stage
 };
@@ -104,6 +142,7 @@ struct Direction {
   uint64_t pool16 = 0;                // total pool size, 16-byte units
   int64_t entries = 0;
   int64_t numItems = 0, numTiles = 0, maxTileK = 0, maxItemRows = 0;
+  FusedTables fused;
 };
 
 // Tiling helpers (the kernels static_assert against the same numbers).

@@ -89,6 +89,13 @@ class Plan:
     def fill_synthetic(self, seed: int):
         capi.check(self.lib.bfCudaPlanFillSynthetic(self.handle, C.c_uint64(seed)), "bfCudaPlanFillSynthetic")
 
+    def set_fused(self, on: bool):
+        """1-RHS applies as one cooperative launch (default) or one launch per stage."""
+        capi.check(self.lib.bfCudaPlanSetFused(self.handle, int(on)), "bfCudaPlanSetFused")
+
+    def is_fused(self, op: int = capi.OP_N) -> bool:
+        return bool(self.lib.bfCudaPlanGetFused(self.handle, op))
+
     def set_profiling(self, on: bool):
         capi.check(self.lib.bfCudaPlanSetProfiling(self.handle, int(on)), "bfCudaPlanSetProfiling")
 

@@ -179,6 +179,16 @@ BfCudaStatus bfCudaPlanSetPerms(BfCudaPlan *plan, const int64_t *inPerm, const i
 BfCudaStatus bfCudaApplyDevice(BfCudaPlan *plan, int32_t op, const void *d_x, int64_t ldx,
                                int64_t nrhs, void *d_y, int64_t ldy, void *stream);
 
+/* One RHS column, whole operator: bfCudaApplyDevice runs the apply as ONE cooperative kernel launch over
+ * "fused" tables — a queue-major copy of the stage tables with a flat workspace, in which the grid-wide
+ * barrier between butterfly levels is replaced by per-buffer readiness counters.  Results are
+ * bit-identical to the per-stage launches (same items, same summation order).  bfCudaPlanSetFused(plan, 0)
+ * switches a plan back to one launch per stage (A/B measurements; the environment variable BF_CUDA_FUSED=0
+ * does the same for every plan); profiled applies (bfCudaPlanSetProfiling) and bfCudaApplyStages always use
+ * per-stage launches.  bfCudaPlanGetFused: 1 if the next 1-RHS apply will be a single launch. */
+BfCudaStatus bfCudaPlanSetFused(BfCudaPlan *plan, int32_t enable);
+int32_t bfCudaPlanGetFused(const BfCudaPlan *plan, int32_t op);
+
 /* Stage-by-stage apply for callers that interleave an exchange between stages (block-row sharding:
  * every rank runs its own leaves of stage s, then rows of the workspace produced for other ranks
  * are exchanged before stage s + 1).  Runs stages [stageBegin, stageEnd) of direction `op`; the

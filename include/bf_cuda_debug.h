@@ -34,6 +34,18 @@ typedef struct BfCudaDebugTables {
   const void *pool;              /* packed values (zeros where val == NULL); NULL if no op carries values */
   int64_t wsArena0Rows, wsArena1Rows; /* ping-pong arenas; rows past them are dedicated (bf_cuda.h) */
   void *owner;                   /* opaque */
+  /* fused single-launch tables (bf_plan.hpp FusedTables): queue-major over all stages, flat workspace rows,
+   * readiness counters.  fusedEnabled == 0: the operator has none (block-row shard, or too large). */
+  int32_t fusedEnabled;
+  uint32_t fusedNumCounters;
+  int64_t fusedWsRows;
+  int64_t fusedNumItems, fusedNumTiles;
+  const void *fusedItems;        /* as `items`; tileBegin indexes fusedTiles; flags bit 1 = jump pseudo item */
+  const void *fusedItemDeps;     /* fusedNumItems x {u32 sig, u32 waitTarget} */
+  const void *fusedTiles;        /* as `tiles`; kc == 0xFFFD: pool cursor jumps to 16 * (rows << 32 | inAddr) */
+  const void *fusedTileDeps;     /* fusedNumTiles x {u32 counter, u32 total} */
+  const uint32_t *fusedQItemBegin; /* [numQueues + 1] */
+  const uint32_t *fusedQTileBegin; /* [numQueues + 1] */
 } BfCudaDebugTables;
 
 BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t op, int32_t numQueues,

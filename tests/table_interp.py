@@ -35,6 +35,15 @@ class Tables:
         self.rows_in, self.rows_out, self.ws_rows = d.rowsIn, d.rowsOut, d.wsRows
         self.cplx = d.dtype == capi.COMPLEX_F64
         self.ws_arena = (int(d.wsArena0Rows), int(d.wsArena1Rows))
+        self.fused = bool(d.fusedEnabled)
+        if self.fused:
+            self.f_items = arr(d.fusedItems, d.fusedNumItems, capi.ITEM_DTYPE)
+            self.f_item_deps = arr(d.fusedItemDeps, d.fusedNumItems, capi.ITEM_DEP_DTYPE)
+            self.f_tiles = arr(d.fusedTiles, d.fusedNumTiles, capi.TILE_DTYPE)
+            self.f_tile_deps = arr(d.fusedTileDeps, d.fusedNumTiles, capi.TILE_DEP_DTYPE)
+            self.f_q_item = arr(d.fusedQItemBegin, Q + 1, np.uint32)
+            self.f_q_tile = arr(d.fusedQTileBegin, Q + 1, np.uint32)
+            self.f_ws_rows, self.f_num_counters = int(d.fusedWsRows), int(d.fusedNumCounters)
 
     def close(self):
         if self._t:
@@ -91,6 +100,101 @@ class Tables:
         for s in range(self.num_stages):
             self.run_stage(space, s)
         return space[1]
+
+    def apply_fused(self, x, order="reverse", seed=0):
+        """The fused single-launch tables (bf_plan.hpp FusedTables) run the way bfGemvStage<., true> runs them:
+        every queue walks its own item list in order, a tile may only be consumed once its operand buffer's
+        counter has reached its total, an accumulating item may only store once its counter has reached the
+        earlier stages' count, and a store bumps the item's counter.  The SCHEDULE is adversarial on purpose
+        (queues visited in reverse / random order, each running until it blocks): a missing dependency shows
+        up as a NaN read from the NaN-initialised flat workspace or as a wrong sum, a cyclic one as a deadlock.
+        Returns (Y, number of times a queue had to wait)."""
+        assert self.fused
+        dt = np.complex128 if self.cplx else np.float64
+        x = np.asarray(x, dtype=dt)
+        if x.ndim == 1:
+            x = x[:, None]
+        nrhs = x.shape[1]
+        nan = np.nan * (1 + 1j) if self.cplx else np.nan
+        space = [x, np.full((self.rows_out, nrhs), nan, dt), np.full((self.f_ws_rows + 2, nrhs), nan, dt)]
+        cnt = np.zeros(max(self.f_num_counters, 1), np.int64)
+        e = 2 if self.cplx else 1
+        Q = self.num_queues
+        cur = self.f_q_item[:-1].astype(np.int64).copy()
+        end = self.f_q_item[1:].astype(np.int64)
+        cpool = np.zeros(Q, np.int64)  # consumer pool cursor per queue, in doubles
+        rng = np.random.default_rng(seed)
+        waits = 0
+        NO = capi.NO_COUNTER
+
+        def try_item(q):
+            """Run the queue's next item if all of its waits are satisfied; False if it has to wait."""
+            i = cur[q]
+            it, dep = self.f_items[i], self.f_item_deps[i]
+            tb, nt, rows = int(it["tileBegin"]), int(it["numTiles"]), int(it["rows"])
+            for t in range(tb, tb + nt):
+                td = self.f_tile_deps[t]
+                if int(td["idx"]) != NO and cnt[int(td["idx"])] < int(td["total"]):
+                    return False
+            acc_flag = int(it["flags"]) & capi.ITEM_ACCUMULATE
+            if acc_flag and int(dep["sig"]) != NO and cnt[int(dep["sig"])] < int(dep["waitTarget"]):
+                return False
+            acc = np.zeros((rows, nrhs), dt)
+            p = cpool[q]
+            for t in range(tb, tb + nt):
+                tl = self.f_tiles[t]
+                kc = int(tl["kc"])
+                if kc == capi.KC_JUMP:
+                    p = ((int(tl["rows"]) << 32) | int(tl["inAddr"])) * 2
+                    continue
+                assert int(tl["rows"]) == rows
+                sp, r = int(tl["inAddr"]) >> 30, int(tl["inAddr"]) & capi.ROW_MASK
+                if kc == capi.KC_IDENTITY:
+                    acc += space[sp][r:r + rows]
+                elif kc == capi.KC_DIAG:
+                    acc += self.pool[p:p + rows, None] * space[sp][r:r + rows]
+                    p += ((rows * 8 + 15) // 16) * 2
+                else:
+                    a = self.pool[p:p + rows * kc * e]
+                    a = a.view(np.complex128) if self.cplx else a
+                    acc += a.reshape(rows, kc) @ space[sp][r:r + kc]
+                    p += ((rows * kc * 8 * e + 15) // 16) * 2
+            cpool[q] = p
+            if not (int(it["flags"]) & capi.ITEM_JUMP):
+                sp, r = int(it["outAddr"]) >> 30, int(it["outAddr"]) & capi.ROW_MASK
+                assert sp != capi.SPACE_X
+                if acc_flag:
+                    space[sp][r:r + rows] += acc
+                else:
+                    space[sp][r:r + rows] = acc
+                if int(dep["sig"]) != NO:
+                    cnt[int(dep["sig"])] += 1
+            cur[q] += 1
+            return True
+
+        while True:
+            live = [q for q in range(Q) if cur[q] < end[q]]
+            if not live:
+                break
+            if order == "reverse":
+                live.reverse()
+            elif order == "random":
+                rng.shuffle(live)
+            progressed = False
+            for q in live:
+                burst = int(rng.integers(1, 6)) if order == "random" else 1 << 30
+                while cur[q] < end[q] and burst > 0:
+                    if not try_item(q):
+                        waits += 1
+                        break
+                    progressed = True
+                    burst -= 1
+            assert progressed, "deadlock: every live queue waits on a counter"
+        # every counter ends at the total its readers wait for
+        for td in self.f_tile_deps:
+            if int(td["idx"]) != NO:
+                assert cnt[int(td["idx"])] == int(td["total"])
+        return space[1], waits
 
     def check_queues(self):
         """Queues partition every stage's items in order; each queue's pool offset is where its

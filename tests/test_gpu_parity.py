@@ -149,3 +149,29 @@ def test_errors_do_not_abort(lib):
             plan.apply_host(np.zeros((50, 1)), capi.OP_T)  # direction not built
         with pytest.raises(ValueError):
             plan.apply_host(np.zeros((41, 1)))
+
+
+@pytest.mark.parametrize("op", [capi.OP_N, capi.OP_T, capi.OP_H])
+def test_single_launch_apply_is_bit_identical_to_per_stage_launches(case, op):
+    """The 1-RHS apply as ONE cooperative launch (fused tables: flat workspace, readiness counters instead of
+    the stage barrier) forms every sum from the same operands in the same order as the per-stage launches.
+    Repeated: the two counter sets alternate between applies."""
+    raw, plan = case
+    cplx = raw.dtype == capi.COMPLEX_F64
+    if op == capi.OP_H and not cplx:
+        pytest.skip("OP_H is complex only")
+    n_in = raw.num_cols if op == capi.OP_N else raw.num_rows
+    x = _x(np.random.default_rng(21), n_in, 1, cplx)
+    plan.set_fused(False)
+    y_staged = plan.apply_host(x, op).copy()
+    stages = plan.last_launch_count
+    plan.set_fused(True)
+    assert plan.is_fused(op), "fused tables missing for a single-GPU plan"
+    for rep in range(5):
+        y = plan.apply_host(x * (rep + 1), op)
+        assert plan.last_launch_count <= 2  # the apply itself (+ the operand staging copy where one is needed)
+        assert np.array_equal(y, y_staged * (rep + 1)) or _relerr(y, y_staged * (rep + 1)) <= 1e-15
+        if rep == 0:
+            assert np.array_equal(y, y_staged), "fused and per-stage results differ"
+    assert stages >= plan.last_launch_count
+    assert _relerr(y_staged, portlib.apply(raw, x, op)) <= TOL

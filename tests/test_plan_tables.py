@@ -45,6 +45,29 @@ def test_tables_match_oracle(name, make, op):
     assert err < 1e-13, err
 
 
+@pytest.mark.parametrize("name,make", CASES)
+@pytest.mark.parametrize("op", [capi.OP_N, capi.OP_T])
+def test_fused_tables_under_adversarial_schedules(name, make, op):
+    """The single-launch tables (readiness counters instead of stage barriers): bit-identical to the stage-major
+    interpretation whatever order the queues run in, no deadlock, no read of an unwritten workspace row."""
+    raw = make()
+    cplx = raw.dtype == capi.COMPLEX_F64
+    rng = np.random.default_rng(12)
+    x = _x(rng, raw.num_cols if op == capi.OP_N else raw.num_rows, 2, cplx)
+    t = Tables(raw, op, num_queues=23)
+    try:
+        assert t.fused
+        y = t.apply(x)
+        for order, seed in (("forward", 0), ("reverse", 0), ("random", 1), ("random", 2)):
+            yf, waits = t.apply_fused(x, order, seed)
+            assert not np.isnan(yf).any()
+            assert np.array_equal(yf, y), order
+            if order == "reverse":
+                assert waits > 0  # the schedule really ran consumers ahead of their producers
+    finally:
+        t.close()
+
+
 def test_queue_count_does_not_change_the_result():
     raw = synth.random_hodbf(n=1024, dtype=capi.COMPLEX_F64, seed=9)
     x = _x(np.random.default_rng(1), raw.num_cols, 1, True)
