@@ -159,7 +159,7 @@ BfCudaStatus bfCudaPlanCreate(const BfCudaPlanDesc *desc, BfCudaPlan **out) {
   P->device = dev;
   P->numSMs = prop.multiProcessorCount;
   P->cooperativeOk = prop.cooperativeLaunch != 0;
-  if (const char *e = std::getenv("BF_CUDA_FUSED")) P->fusedEnabled = std::atoi(e) != 0;
+  if (const char *e = std::getenv("BF_CUDA_FUSED")) P->fusedMode = std::atoi(e) != 0 ? 1 : 0;
   P->dtype = desc->dtype;
   P->numRows = desc->numRows;
   P->numCols = desc->numCols;
@@ -234,11 +234,12 @@ BfCudaStatus bfCudaPlanSetProfiling(BfCudaPlan *P, int32_t enable) {
 
 BfCudaStatus bfCudaPlanSetFused(BfCudaPlan *P, int32_t enable) {
   if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
-  P->fusedEnabled = enable != 0;
+  P->fusedMode = enable < 0 ? 2 : (enable != 0 ? 1 : 0);
   return BF_CUDA_OK;
 }
 int32_t bfCudaPlanGetFused(const BfCudaPlan *P, int32_t op) {
-  return P && op >= 0 && op <= 2 && P->dir[op].built && P->dir[op].fusedReady && P->cooperativeOk && P->fusedEnabled && !P->profiling;
+  if (!P || op < 0 || op > 2 || !P->dir[op].built || !P->dir[op].fusedReady || !P->cooperativeOk || P->profiling) return 0;
+  return P->fusedMode == 1 || (P->fusedMode == 2 && (uint64_t)P->dir[op].host.pool16 * 16ull >= kFusedMinPoolBytes);
 }
 
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *P) { return P ? P->lastLaunches : 0; }
@@ -297,12 +298,28 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
   const int32_t *scatterOut = op == BF_CUDA_OP_N ? P->outPerm : P->invInPerm;
 
   // 1 RHS, whole apply: ONE cooperative launch over the fused tables (flat workspace, readiness counters)
-  const bool fused = nrhs == 1 && dd.fusedReady && P->cooperativeOk && P->fusedEnabled && !P->profiling && !staged;
+  // Measured A/B (tools/fused_ab.py, profiles/r2c_fused_ab.jsonl): 10.87 -> 10.66 ms at N = 524 288 (0.942 -> 0.961
+  // of the HBM peak), but 0.591 -> 0.613 ms at 65 536 and 0.152 -> 0.189 ms at 16 384, where a stage is a handful of
+  // tiles per warp and the hand-over through counters costs more than the PDL-chained launches; hence the size
+  // switch (fusedMode: 0 never, 1 always, 2 = operators whose pool is at least kFusedMinPoolBytes).
+  const bool fusedWanted = P->fusedMode == 1 || (P->fusedMode == 2 && (uint64_t)D.pool16 * 16ull >= kFusedMinPoolBytes);
+  const bool fused = nrhs == 1 && dd.fusedReady && P->cooperativeOk && fusedWanted && !P->profiling && !staged;
   // column chunking keeps the workspace within budget
   const size_t rowsPad = (size_t)(fused ? std::max(D.wsRows, dd.fusedWsRows) : D.wsRows) + 2;
   const size_t xRowsPad = (size_t)D.rowsIn + 2;
   int64_t chunk = nrhs;
-  while (chunk > 1 && (rowsPad + xRowsPad) * (size_t)chunk * es > P->maxScratchBytes) chunk = (chunk + 1) / 2;
+  // the budget: what the device has free (plus what the plan already holds for this purpose) minus a margin,
+  // so a 256-column block runs as ONE chunk whenever the memory is there — every extra chunk re-reads the pool
+  size_t budget = P->maxScratchBytes;
+  if ((rowsPad + xRowsPad) * (size_t)nrhs * es > P->scratchBytes) {
+    size_t freeB = 0, totalB = 0;
+    if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
+      const size_t margin = size_t(2) << 30;
+      const size_t avail = freeB + P->scratchBytes > margin ? freeB + P->scratchBytes - margin : 0;
+      budget = std::min(budget, avail);
+    }
+  }
+  while (chunk > 1 && (rowsPad + xRowsPad) * (size_t)chunk * es + 512 > budget) chunk = (chunk + 1) / 2;
   const size_t wsBytes = ((rowsPad * (size_t)chunk * es + 255) / 256) * 256;
   const size_t need = wsBytes + xRowsPad * (size_t)chunk * es + 256;
   if (P->scratchBytes < need) {

@@ -72,6 +72,7 @@ struct DevDirection {
 } // namespace bfc
 
 constexpr size_t kStageBytes = size_t(8) << 20; // one pinned staging buffer
+constexpr uint64_t kFusedMinPoolBytes = 24ull << 30; // single-launch 1-RHS apply from this pool size on (bf_capi.cu applyImpl)
 
 struct BfCudaPlan {
   int device = 0;
@@ -95,8 +96,8 @@ struct BfCudaPlan {
   bool profiling = false;
   std::vector<cudaEvent_t> events;
   int64_t lastStages = 0;
-  size_t maxScratchBytes = size_t(24) << 30;
+  size_t maxScratchBytes = size_t(96) << 30; // upper bound of the workspace; the real budget is the free memory (applyImpl)
   bool cooperativeOk = false; // device supports cooperative launches (the fused 1-RHS apply needs co-resident CTAs)
-  bool fusedEnabled = true;   // bfCudaPlanSetFused / BF_CUDA_FUSED=0: per-stage launches only (A/B measurements)
+  int fusedMode = 2;          // bfCudaPlanSetFused / BF_CUDA_FUSED: 0 per-stage launches, 1 single launch, 2 by size
 };
 

@@ -182,10 +182,13 @@ BfCudaStatus bfCudaApplyDevice(BfCudaPlan *plan, int32_t op, const void *d_x, in
 /* One RHS column, whole operator: bfCudaApplyDevice runs the apply as ONE cooperative kernel launch over
  * "fused" tables — a queue-major copy of the stage tables with a flat workspace, in which the grid-wide
  * barrier between butterfly levels is replaced by per-buffer readiness counters.  Results are
- * bit-identical to the per-stage launches (same items, same summation order).  bfCudaPlanSetFused(plan, 0)
- * switches a plan back to one launch per stage (A/B measurements; the environment variable BF_CUDA_FUSED=0
- * does the same for every plan); profiled applies (bfCudaPlanSetProfiling) and bfCudaApplyStages always use
- * per-stage launches.  bfCudaPlanGetFused: 1 if the next 1-RHS apply will be a single launch. */
+ * bit-identical to the per-stage launches (same items, same summation order).  By default the single launch is
+ * used from a pool size on where it measures faster (24 GiB: 0.942 -> 0.961 of the HBM peak at N = 524 288; on
+ * small operators a stage is a few tiles per warp and the PDL-chained per-stage launches win).
+ * bfCudaPlanSetFused(plan, 0 / 1 / -1) = never / always / by size (A/B measurements; the environment variable
+ * BF_CUDA_FUSED=0/1 does the same for every plan); profiled applies (bfCudaPlanSetProfiling) and
+ * bfCudaApplyStages always use per-stage launches.  bfCudaPlanGetFused: 1 if the next 1-RHS apply will be a
+ * single launch. */
 BfCudaStatus bfCudaPlanSetFused(BfCudaPlan *plan, int32_t enable);
 int32_t bfCudaPlanGetFused(const BfCudaPlan *plan, int32_t op);
 

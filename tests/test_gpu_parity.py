@@ -139,7 +139,13 @@ def test_device_api_and_launch_count():
         plan.apply_device(xd, yd, stream=torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         assert _relerr(yd.cpu().numpy(), portlib.apply(raw, x)) <= TOL
-        assert plan.last_launch_count == plan.info["numStagesN"]
+        # one cooperative launch for the whole apply, or one launch per stage
+        assert plan.last_launch_count == (1 if plan.is_fused() else plan.info["numStagesN"])
+        plan.set_fused(not plan.is_fused())
+        y2 = torch.empty_like(yd)
+        plan.apply_device(xd, y2, stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert torch.equal(y2, yd)
 
 
 def test_errors_do_not_abort(lib):
