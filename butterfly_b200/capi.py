@@ -186,6 +186,7 @@ EXPORTED_SYMBOLS = [
     "bfCudaGmresProject",
     "bfCudaGmresSubtract",
     "bfCudaGmresScale",
+    "bfCudaGmresProjectStatic",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
@@ -308,6 +309,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaGmresProject.restype = i32
     lib.bfCudaGmresSubtract.argtypes = [vp, i64, i64, vp, vp, i64, vp, vp, vp]
     lib.bfCudaGmresSubtract.restype = i32
+    lib.bfCudaGmresProjectStatic.argtypes = [vp, i64, i64, vp, i64, vp, vp]
+    lib.bfCudaGmresProjectStatic.restype = i32
     lib.bfCudaGmresScale.argtypes = [vp, i64, vp, vp, vp, vp]
     lib.bfCudaGmresScale.restype = i32
     lib.bfCudaAbiVersion.argtypes = []

@@ -17,10 +17,15 @@
 
 #include <cmath>
 #include <complex>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "bf_cuda.h"
+
+namespace bfc {
+BfCudaStatus fail(BfCudaStatus st, const std::string &msg); // bf_capi.cu: records bfCudaLastErrorMessage
+}
 
 namespace {
 constexpr int kBlocks = 148 * 4;
@@ -390,4 +395,74 @@ extern "C" BfCudaStatus bfCudaGmresScale(const void *w, int64_t n, const void *n
   if (n < 0 || !w || !nrm2 || !dst) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   gmresScale<<<kBlocks, kThreads, 0, (cudaStream_t)stream>>>((const double2 *)w, n, (const double2 *)nrm2, (double2 *)dst, (double2 *)dst2);
   return cudaGetLastError() == cudaSuccess ? BF_CUDA_OK : BF_CUDA_ERROR_RUNTIME;
+}
+
+// ---- allocation-free variant of bfCudaGmresProject ------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The partial sums
+// live in a file-scope device array instead of a caller-provided scratch buffer: kBlocks x (maxM + 2) double2 =
+// 606 208 bytes, held by every GPU that loads the library until the process exits.
+//
+// In HOST code the array's name is a host-side stand-in, not a device address (a kernel handed it faults, or —
+// where the GPU can reach host memory — silently uses the wrong memory), so the address is asked for once per
+// device with that device current (cudaGetSymbolAddress, return code checked) and only that pointer is ever
+// passed to a kernel.  The call path below contains no cudaMalloc / cudaFree / allocating library routine.
+//
+// All calls on a device SHARE the array: two calls that overlap on the GPU (different streams, no dependency
+// between them) race on it — serialise them.  The array keeps the previous call's contents; nothing needs
+// clearing, because every slot gmresFinalize reads (m + 1 rows of kBlocks partials) is written by the
+// gmresProjectPartial launches of the SAME call before it, in stream order.
+namespace {
+constexpr int64_t kStaticProjectMaxM = BF_CUDA_GMRES_PROJECT_STATIC_MAX_M;
+constexpr size_t kStaticScratchBytes = sizeof(double2) * (size_t)kBlocks * (size_t)(kStaticProjectMaxM + 2);
+static __device__ __align__(256) unsigned char g_projectScratch[kStaticScratchBytes];
+
+constexpr int kMaxScratchDevices = 64;
+double2 *g_projectScratchAddr[kMaxScratchDevices]; // per device ordinal; NULL = not asked for yet
+std::mutex g_projectScratchMutex;
+
+// Device address of g_projectScratch on the CURRENT device (looked up once per device).
+BfCudaStatus staticProjectScratch(double2 **ptr) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxScratchDevices)
+    return bfc::fail(BF_CUDA_ERROR_NO_DEVICE, "bfCudaGmresProjectStatic: no current CUDA device");
+  std::lock_guard<std::mutex> lock(g_projectScratchMutex);
+  if (!g_projectScratchAddr[dev]) {
+    double2 *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_projectScratch); // `dev` is current
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return bfc::fail(BF_CUDA_ERROR_RUNTIME, std::string("bfCudaGmresProjectStatic: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    }
+    g_projectScratchAddr[dev] = p;
+  }
+  *ptr = g_projectScratchAddr[dev];
+  return BF_CUDA_OK;
+}
+} // namespace
+
+extern "C" BfCudaStatus bfCudaGmresProjectStatic(const void *V, int64_t ldv, int64_t m, const void *w, int64_t n, void *out,
+                                                 void *stream) {
+  if (m < 0 || n < 0 || !w || !out || (m > 0 && !V))
+    return bfc::fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "bfCudaGmresProjectStatic: null operand or negative size");
+  if (m > kStaticProjectMaxM)
+    return bfc::fail(BF_CUDA_ERROR_INVALID_ARGUMENT,
+                     "bfCudaGmresProjectStatic: m = " + std::to_string(m) + " basis vectors exceed the static scratch (maximum " +
+                         std::to_string(kStaticProjectMaxM) + "); use bfCudaGmresProject with a caller-provided scratch buffer");
+  double2 *part = nullptr;
+  const BfCudaStatus st = staticProjectScratch(&part);
+  if (st != BF_CUDA_OK) return st;
+  cudaStream_t s = (cudaStream_t)stream;
+  const double2 *Vd = (const double2 *)V;
+  // the same launches as bfCudaGmresProject: chunks of kProjChunk basis vectors per sweep, |w|^2 into slot m
+  for (int64_t i0 = 0; i0 == 0 || i0 < m; i0 += kProjChunk) {
+    const int mc = (int)std::min<int64_t>(kProjChunk, m - i0);
+    const bool last = i0 + kProjChunk >= m;
+    gmresProjectPartial<<<kBlocks, kThreads, 0, s>>>(Vd ? Vd + i0 * ldv : nullptr, ldv, mc, (const double2 *)w, n,
+                                                     part + i0 * kBlocks, last ? mc : -1);
+  }
+  gmresFinalize<<<(unsigned)(m + 1), kThreads, 0, s>>>(part, kBlocks, (double2 *)out);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return bfc::fail(BF_CUDA_ERROR_RUNTIME, std::string("bfCudaGmresProjectStatic: launch: ") + cudaGetErrorString(e));
+  return BF_CUDA_OK;
 }

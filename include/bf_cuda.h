@@ -253,6 +253,22 @@ BfCudaStatus bfCudaGmresSubtract(const void *V, int64_t ldv, int64_t m, const vo
 BfCudaStatus bfCudaGmresScale(const void *w, int64_t n, const void *nrm2, void *dst, void *dst2,
                               void *stream);
 
+/* Allocation-free variant of bfCudaGmresProject.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and results as bfCudaGmresProject, minus `scratch`: the
+ * partial sums live in a static device array inside the library (606 208 bytes, held by every GPU that loads
+ * the library until the process exits), looked up once per device with cudaGetSymbolAddress; the call issues no
+ * cudaMalloc / cudaFree / allocating library routine.  Limits and rules:
+ *   - m <= BF_CUDA_GMRES_PROJECT_STATIC_MAX_M basis vectors; a larger m is refused with
+ *     BF_CUDA_ERROR_INVALID_ARGUMENT and a message in bfCudaLastErrorMessage (use bfCudaGmresProject then);
+ *   - V, w, out must live on the CURRENT device;
+ *   - every call on a device shares the one array: calls that overlap on the GPU (different streams, no
+ *     dependency between them) RACE — serialise them.  The array keeps the last call's contents; nothing has to
+ *     be cleared, every slot read is written earlier in the same call. */
+#define BF_CUDA_GMRES_PROJECT_STATIC_MAX_M 62
+BfCudaStatus bfCudaGmresProjectStatic(const void *V, int64_t ldv, int64_t m, const void *w, int64_t n,
+                                      void *out, void *stream);
+
 /* Number of kernel launches the last apply on this plan issued (bench.py's gpu_launches). */
 int64_t bfCudaPlanLastLaunchCount(const BfCudaPlan *plan);
 
