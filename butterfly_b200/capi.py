@@ -18,7 +18,7 @@ LIB_DIR = PKG_DIR / "lib"
 LIB_PATH = LIB_DIR / "libbfcuda.so"
 ATTACH_LIB_PATH = LIB_DIR / "libbfcuda_attach.so"
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # enums (include/bf_cuda.h)
 OK = 0
@@ -78,6 +78,8 @@ class PlanDesc(C.Structure):
         ("ops", C.POINTER(RawOp)),
         ("device", C.c_int32),
         ("buildTranspose", C.c_int32),
+        ("shardWorld", C.c_int32),
+        ("shardRank", C.c_int32),
     ]
 
 
@@ -147,7 +149,38 @@ class DebugTables(C.Structure):
         ("fusedTileDeps", C.c_void_p),
         ("fusedQItemBegin", C.POINTER(C.c_uint32)),
         ("fusedQTileBegin", C.POINTER(C.c_uint32)),
+        ("itemPeers", C.POINTER(C.c_uint32)),
+        ("stageRecvMask", C.POINTER(C.c_uint32)),
+        ("stageSendMask", C.POINTER(C.c_uint32)),
     ]
+
+
+class ShardHandle(C.Structure):
+    """struct BfCudaShardHandle"""
+
+    _fields_ = [
+        ("pid", C.c_int64), ("device", C.c_int32), ("rank", C.c_int32), ("wsBytes", C.c_int64),
+        ("wsPtr", C.c_void_p), ("flagsPtr", C.c_void_p), ("hasIpc", C.c_int32), ("reserved", C.c_int32),
+        ("wsIpc", C.c_ubyte * 64), ("flagsIpc", C.c_ubyte * 64),
+    ]
+
+
+class ShardedInfo(C.Structure):
+    """struct BfCudaShardedInfo"""
+
+    _fields_ = [
+        ("world", C.c_int32), ("mode", C.c_int32), ("numRows", C.c_int64), ("numCols", C.c_int64),
+        ("numEntries", C.c_int64), ("maxRankEntries", C.c_int64), ("poolBytesMax", C.c_int64),
+        ("sentRowsPerApply", C.c_int64), ("numStages", C.c_int64), ("yCuts", C.c_int64 * 17),
+    ]
+
+    def as_dict(self):
+        d = {n: getattr(self, n) for n, _ in self._fields_ if n != "yCuts"}
+        d["yCuts"] = list(self.yCuts)[: self.world + 1]
+        return d
+
+
+SHARD_RHS_COLS, SHARD_BLOCK_ROWS = 0, 1
 
 
 ITEM_DTYPE = np.dtype([("outAddr", "<u4"), ("tileBegin", "<u4"), ("rows", "<u2"), ("flags", "<u2"), ("numTiles", "<u4")])
@@ -187,6 +220,29 @@ EXPORTED_SYMBOLS = [
     "bfCudaGmresSubtract",
     "bfCudaGmresScale",
     "bfCudaGmresProjectStatic",
+    "bfCudaShardDescsCreate",
+    "bfCudaShardDescsGet",
+    "bfCudaShardDescsGetLayout",
+    "bfCudaShardDescsFree",
+    "bfCudaShardRankCreate",
+    "bfCudaShardRankDestroy",
+    "bfCudaShardRankGetPlan",
+    "bfCudaShardRankSentRows",
+    "bfCudaShardRankGetHandle",
+    "bfCudaShardRankConnect",
+    "bfCudaShardRankApplyDevice",
+    "bfCudaShardRankApplyStages",
+    "bfCudaCommInit",
+    "bfCudaCommDestroy",
+    "bfCudaCommSize",
+    "bfCudaPlanShard",
+    "bfCudaShardedPlanDestroy",
+    "bfCudaShardedPlanGetInfo",
+    "bfCudaShardedPlanGetRankPlan",
+    "bfCudaShardedApplyHost",
+    "bfCudaShardedApplyDevice",
+    "bfCudaShardedSynchronize",
+    "bfCudaShardedRankStream",
     "bfCudaPlanSetProfiling",
     "bfCudaPlanGetStageTimes",
     "bfCudaPlanGetStageEntries",
@@ -313,6 +369,53 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaGmresProjectStatic.restype = i32
     lib.bfCudaGmresScale.argtypes = [vp, i64, vp, vp, vp, vp]
     lib.bfCudaGmresScale.restype = i32
+    PD = C.POINTER(PlanDesc)
+    lib.bfCudaShardDescsCreate.argtypes = [PD, i32, C.POINTER(C.c_double), C.POINTER(vp)]
+    lib.bfCudaShardDescsCreate.restype = i32
+    lib.bfCudaShardDescsGet.argtypes = [vp, i32]
+    lib.bfCudaShardDescsGet.restype = PD
+    lib.bfCudaShardDescsGetLayout.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), C.POINTER(i64), C.POINTER(i64)]
+    lib.bfCudaShardDescsGetLayout.restype = i32
+    lib.bfCudaShardDescsFree.argtypes = [vp]
+    lib.bfCudaShardDescsFree.restype = None
+    lib.bfCudaShardRankCreate.argtypes = [PD, C.POINTER(vp)]
+    lib.bfCudaShardRankCreate.restype = i32
+    lib.bfCudaShardRankDestroy.argtypes = [vp]
+    lib.bfCudaShardRankDestroy.restype = i32
+    lib.bfCudaShardRankGetPlan.argtypes = [vp]
+    lib.bfCudaShardRankGetPlan.restype = vp
+    lib.bfCudaShardRankSentRows.argtypes = [vp]
+    lib.bfCudaShardRankSentRows.restype = i64
+    lib.bfCudaShardRankGetHandle.argtypes = [vp, C.POINTER(ShardHandle)]
+    lib.bfCudaShardRankGetHandle.restype = i32
+    lib.bfCudaShardRankConnect.argtypes = [vp, C.POINTER(ShardHandle)]
+    lib.bfCudaShardRankConnect.restype = i32
+    lib.bfCudaShardRankApplyDevice.argtypes = [vp, vp, vp, vp]
+    lib.bfCudaShardRankApplyDevice.restype = i32
+    lib.bfCudaShardRankApplyStages.argtypes = [vp, vp, vp, i64, i64, vp]
+    lib.bfCudaShardRankApplyStages.restype = i32
+    lib.bfCudaCommInit.argtypes = [i32, C.POINTER(i32), C.POINTER(vp)]
+    lib.bfCudaCommInit.restype = i32
+    lib.bfCudaCommDestroy.argtypes = [vp]
+    lib.bfCudaCommDestroy.restype = i32
+    lib.bfCudaCommSize.argtypes = [vp]
+    lib.bfCudaCommSize.restype = i32
+    lib.bfCudaPlanShard.argtypes = [PD, vp, i32, C.POINTER(C.c_double), C.POINTER(vp)]
+    lib.bfCudaPlanShard.restype = i32
+    lib.bfCudaShardedPlanDestroy.argtypes = [vp]
+    lib.bfCudaShardedPlanDestroy.restype = i32
+    lib.bfCudaShardedPlanGetInfo.argtypes = [vp, C.POINTER(ShardedInfo)]
+    lib.bfCudaShardedPlanGetInfo.restype = i32
+    lib.bfCudaShardedPlanGetRankPlan.argtypes = [vp, i32]
+    lib.bfCudaShardedPlanGetRankPlan.restype = vp
+    lib.bfCudaShardedApplyHost.argtypes = [vp, i32, vp, i64, i64, vp, i64]
+    lib.bfCudaShardedApplyHost.restype = i32
+    lib.bfCudaShardedApplyDevice.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    lib.bfCudaShardedApplyDevice.restype = i32
+    lib.bfCudaShardedSynchronize.argtypes = [vp]
+    lib.bfCudaShardedSynchronize.restype = i32
+    lib.bfCudaShardedRankStream.argtypes = [vp, i32]
+    lib.bfCudaShardedRankStream.restype = vp
     lib.bfCudaAbiVersion.argtypes = []
     lib.bfCudaAbiVersion.restype = i32
     if path is None:

@@ -70,6 +70,13 @@ static BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
   } else {
     BF_CUDA_TRY(cudaMemset(dd.pool, 0, poolBytes));
   }
+  if (D.shardWorld > 1) { // block-row shard: which ranks read which item's rows
+    std::vector<uint32_t> peers;
+    peers.reserve(nI);
+    for (const Stage &S : D.stages) peers.insert(peers.end(), S.itemPeers.begin(), S.itemPeers.end());
+    BF_CUDA_TRY(cudaMalloc(&dd.itemPeers, std::max<size_t>(nI, 1) * sizeof(uint32_t)));
+    if (nI) BF_CUDA_TRY(cudaMemcpy(dd.itemPeers, peers.data(), nI * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  }
   // fused single-launch tables (1-RHS apply): uploaded once, host copies dropped
   FusedTables &F = D.fused;
   if (F.enabled) {
@@ -303,7 +310,7 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
   // tiles per warp and the hand-over through counters costs more than the PDL-chained launches; hence the size
   // switch (fusedMode: 0 never, 1 always, 2 = operators whose pool is at least kFusedMinPoolBytes).
   const bool fusedWanted = P->fusedMode == 1 || (P->fusedMode == 2 && (uint64_t)D.pool16 * 16ull >= kFusedMinPoolBytes);
-  const bool fused = nrhs == 1 && dd.fusedReady && P->cooperativeOk && fusedWanted && !P->profiling && !staged;
+  const bool fused = nrhs == 1 && dd.fusedReady && P->cooperativeOk && fusedWanted && !P->profiling && !staged && D.shardWorld <= 1;
   // column chunking keeps the workspace within budget
   const size_t rowsPad = (size_t)(fused ? std::max(D.wsRows, dd.fusedWsRows) : D.wsRows) + 2;
   const size_t xRowsPad = (size_t)D.rowsIn + 2;
@@ -320,7 +327,16 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
     }
   }
   while (chunk > 1 && (rowsPad + xRowsPad) * (size_t)chunk * es + 512 > budget) chunk = (chunk + 1) / 2;
-  const size_t wsBytes = ((rowsPad * (size_t)chunk * es + 255) / 256) * 256;
+  const bool sharded = D.shardWorld > 1;
+  if (sharded) {
+    // one rank of a block-row sharded operator: peers store into the workspace, so it is the externally owned,
+    // peer-mapped region, and the hand-over protocol (bf_kernels.cu) is written for one column per apply
+    if (!P->shardDev || !P->extWs) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "a block-row shard is applied through bfCudaShardRankApply / bfCudaShardedApply* (its peers must be connected)");
+    if (nrhs != 1) return fail(BF_CUDA_ERROR_NOT_IMPLEMENTED, "a block-row shard applies one column per call");
+    if (rowsPad * es > P->extWsBytes) return fail(BF_CUDA_ERROR_RUNTIME, "exchange workspace smaller than the plan's workspace");
+    chunk = 1;
+  }
+  const size_t wsBytes = sharded ? 0 : ((rowsPad * (size_t)chunk * es + 255) / 256) * 256;
   const size_t need = wsBytes + xRowsPad * (size_t)chunk * es + 256;
   if (P->scratchBytes < need) {
     BF_CUDA_TRY(cudaStreamSynchronize(stream));
@@ -343,7 +359,7 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
     StageLaunch a{};
     a.pool = dd.pool;
     a.base[kSpaceY] = yp; a.ld[kSpaceY] = ldy;
-    a.base[kSpaceW] = P->scratch; a.ld[kSpaceW] = nc;
+    a.base[kSpaceW] = sharded ? P->extWs : P->scratch; a.ld[kSpaceW] = nc;
     a.outPerm = scatterOut;
     a.numQueues = D.numQueues; a.nrhs = (int)nc; a.colBegin = 0;
     // overlap a stage's prologue with the previous stage's tail where stages are short (bf_kernels.cu)
@@ -389,7 +405,14 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
       a.qItemBegin = dd.qItemBegin + s * (Q + 1);
       a.qTileBegin = dd.qTileBegin + s * (Q + 1);
       a.qPool16 = dd.qPool16 + s * (Q + 1);
-      cudaError_t e = nc == 1 ? launchGemvStage(P->dtype, a, P->numSMs, stream) : launchWideStage(P->dtype, a, P->numSMs, stream);
+      if (sharded) {
+        a.shard = P->shardDev;
+        a.itemPeers = dd.itemPeers + dd.itemOff[s];
+        a.stage = (int)s;
+        a.epoch = P->shardEpoch;
+      }
+      cudaError_t e = sharded ? launchGemvShardStage(P->dtype, a, stream)
+                              : (nc == 1 ? launchGemvStage(P->dtype, a, P->numSMs, stream) : launchWideStage(P->dtype, a, P->numSMs, stream));
       if (e != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("stage launch: ") + cudaGetErrorString(e));
       ++launches;
     }

@@ -19,6 +19,7 @@ struct Owner {
   std::vector<uint32_t> qItemBegin, qTileBegin;
   std::vector<int32_t> tileRow0, tileCol0;
   std::vector<unsigned char> pool;
+  std::vector<uint32_t> itemPeers, recvMask, sendMask;
   BfCudaDebugTables t;
 };
 } // namespace
@@ -77,6 +78,16 @@ extern "C" BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t o
   t.fusedItems = F.items.data(); t.fusedItemDeps = F.itemDeps.data();
   t.fusedTiles = F.tiles.data(); t.fusedTileDeps = F.tileDeps.data();
   t.fusedQItemBegin = F.qItemBegin.data(); t.fusedQTileBegin = F.qTileBegin.data();
+  if (D.shardWorld > 1) {
+    for (const Stage &S : D.stages) {
+      o->itemPeers.insert(o->itemPeers.end(), S.itemPeers.begin(), S.itemPeers.end());
+      o->recvMask.push_back(S.recvMask);
+      o->sendMask.push_back(S.sendMask);
+    }
+    t.itemPeers = o->itemPeers.data();
+    t.stageRecvMask = o->recvMask.data();
+    t.stageSendMask = o->sendMask.data();
+  }
   *out = &t;
   return BF_CUDA_OK;
 }

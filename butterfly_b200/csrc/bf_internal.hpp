@@ -55,6 +55,7 @@ struct DevDirection {
   ItemDep *fItemDeps = nullptr;
   TileDep *fTileDeps = nullptr;
   uint32_t *fqItemBegin = nullptr, *fqTileBegin = nullptr;
+  uint32_t *itemPeers = nullptr; // block-row shards: per item (all stages concatenated like `items`), ranks that read its rows
   uint32_t *counters = nullptr; // [2][numCounters]
   uint32_t numCounters = 0;
   int64_t fusedWsRows = 0;
@@ -62,7 +63,8 @@ struct DevDirection {
   void release() {
     cudaFree(items); cudaFree(tiles); cudaFree(qItemBegin); cudaFree(qTileBegin); cudaFree(qPool16); cudaFree(pool);
     cudaFree(fItems); cudaFree(fTiles); cudaFree(fItemDeps); cudaFree(fTileDeps); cudaFree(fqItemBegin); cudaFree(fqTileBegin);
-    cudaFree(counters);
+    cudaFree(counters); cudaFree(itemPeers);
+    itemPeers = nullptr;
     items = nullptr; tiles = nullptr; qItemBegin = qTileBegin = nullptr; qPool16 = nullptr; pool = nullptr;
     fItems = nullptr; fTiles = nullptr; fItemDeps = nullptr; fTileDeps = nullptr; fqItemBegin = fqTileBegin = nullptr;
     counters = nullptr;
@@ -98,6 +100,12 @@ struct BfCudaPlan {
   int64_t lastStages = 0;
   size_t maxScratchBytes = size_t(96) << 30; // upper bound of the workspace; the real budget is the free memory (applyImpl)
   bool cooperativeOk = false; // device supports cooperative launches (the fused 1-RHS apply needs co-resident CTAs)
+  // block-row shard (bf_comm.cu): the workspace lives in memory the peers can store into, and every stage kernel
+  // gets the hand-over context; one column per apply, `shardEpoch` counts them
+  unsigned char *extWs = nullptr;      // not owned
+  size_t extWsBytes = 0;
+  const bfc::ShardLaunch *shardDev = nullptr; // device copy, not owned
+  uint32_t shardEpoch = 0;
   int fusedMode = 2;          // bfCudaPlanSetFused / BF_CUDA_FUSED: 0 per-stage launches, 1 single launch, 2 by size
 };
 

@@ -144,8 +144,15 @@ __device__ __forceinline__ void tileFma(typename Scalar<CPLX>::T (&acc)[P], cons
 // else to do, in which case it spins: all CTAs are co-resident (cooperative launch, one CTA per SM) and every
 // wait is on items of an EARLIER stage, which a warp reaches without waiting on anything of this one, so the
 // spin always ends.  The counters of the NEXT apply are zeroed here (two sets, alternating).
-template <bool CPLX, bool FUSED>
+//
+// SHARDED (MODE 2) = one stage of one rank of a block-row sharded operator (ShardLaunch): before it touches the
+// workspace every warp waits for the flags of the ranks that pushed rows to this one during the previous stage
+// (stage 0: for every peer to have finished the previous apply — the workspace is about to be overwritten);
+// an item whose rows another rank reads stores them into that rank's workspace as well; the last warp of the
+// grid to finish posts this stage's flag to every peer.
+template <bool CPLX, int MODE>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid_constant__ StageLaunch a) {
+  constexpr bool FUSED = MODE == 1, SHARDED = MODE == 2;
   using S = Scalar<CPLX>;
   using T = typename S::T;
   constexpr int ES = CPLX ? 16 : 8;
@@ -181,10 +188,53 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   if (FUSED) { // zero the counter set of the next apply (the previous user of that set has completed: stream order)
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.numCounters; i += gridDim.x * blockDim.x) a.cntNext[i] = 0u;
   }
-  if (q >= a.numQueues) { pdlSync(); return; }
+  // block-row shard: hand-over between ranks
+  auto shardWait = [&]() { // rows pushed by peers during the previous stage have landed (flags are written after them)
+    if (!SHARDED) return;
+    const ShardLaunch &sh = *a.shard;
+    if (lane == 0) {
+      // stage 0 waits for EVERY peer to have finished the previous apply (their last stage's flag, epoch - 1)
+      const int ws = a.stage == 0 ? sh.numStages - 1 : a.stage - 1;
+      const uint32_t want = a.stage == 0 ? a.epoch - 1u : a.epoch;
+      uint32_t mask = a.stage == 0 ? ((1u << sh.world) - 1u) & ~(1u << sh.rank) : sh.recvMask[ws];
+      const uint32_t *flags = sh.peerFlags[sh.rank] + (size_t)ws * sh.world;
+      for (; mask; mask &= mask - 1) {
+        const int r = __ffs(mask) - 1;
+        unsigned long long spins = 0;
+        uint32_t v;
+        do {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+          if ((int32_t)(v - want) >= 0) break;
+          if (++spins > (1ull << 26)) __trap(); // a peer that never arrives: fail loudly instead of hanging
+          __nanosleep(64);
+        } while (true);
+      }
+      fenceProxyAsyncGlobal(); // peer stores (generic proxy, another GPU) -> this thread's bulk copies
+    }
+    __syncwarp();
+  };
+  auto shardDone = [&]() { // this warp's stores (local and to peers) are complete; the last warp posts the flags
+    if (!SHARDED) return;
+    __syncwarp();
+    if (lane == 0) {
+      const ShardLaunch &sh = *a.shard;
+      __threadfence_system();
+      const uint32_t old = atomicAdd(sh.done + a.stage, 1u);
+      if ((old + 1u) % sh.totalWarps == 0u) {
+        __threadfence_system();
+        for (int r = 0; r < sh.world; ++r)
+          if (r != sh.rank) {
+            uint32_t *f = sh.peerFlags[r] + (size_t)a.stage * sh.world + sh.rank;
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.epoch) : "memory");
+          }
+      }
+    }
+  };
+  // (every warp waits, also one without work: the NEXT stage relies on this grid having seen the previous pushes)
+  if (q >= a.numQueues) { pdlSync(); shardWait(); shardDone(); return; }
   const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
   const uint32_t tBeg = a.qTileBegin[q], tEnd = a.qTileBegin[q + 1];
-  if (iBeg == iEnd) { pdlSync(); return; }
+  if (iBeg == iEnd) { pdlSync(); shardWait(); shardDone(); return; }
   const uint64_t pol = policyEvictFirst();
 
   // Descriptor windows: lane l holds tiles[twBase + l] / tiles[twBase + 32 + l] (and the same for
@@ -198,7 +248,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   const uint64_t *tileDepTab = reinterpret_cast<const uint64_t *>(a.tileDeps);
   const uint64_t *itemDepTab = reinterpret_cast<const uint64_t *>(a.itemDeps);
   auto loadTileDeps = [&](uint32_t base) -> uint64_t { return (FUSED && base + lane < tEnd) ? tileDepTab[base + lane] : ~0ull; };
-  auto loadItemDeps = [&](uint32_t base) -> uint64_t { return (FUSED && base + lane < iEnd) ? itemDepTab[base + lane] : ~0ull; };
+  auto loadItemDeps = [&](uint32_t base) -> uint64_t {
+    if (FUSED) return base + lane < iEnd ? itemDepTab[base + lane] : ~0ull;
+    if (SHARDED) return base + lane < iEnd ? (uint64_t)a.itemPeers[base + lane] : 0ull; // ranks that read the item's rows
+    return ~0ull;
+  };
   uint32_t twBase = tBeg, iwBase = iBeg;
   uint64_t tw0 = loadTiles(twBase), tw1 = loadTiles(twBase + 32);
   uint4 iw0 = loadItems(iwBase), iw1 = loadItems(iwBase + 32);
@@ -224,10 +278,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   auto getItem = [&](uint32_t i) -> DevItem {
     if (i - iwBase >= 32) {
       iw0 = iw1; iwBase += 32; iw1 = loadItems(iwBase + 32);
-      if (FUSED) { id0 = id1; id1 = loadItemDeps(iwBase + 32); }
+      if (FUSED || SHARDED) { id0 = id1; id1 = loadItemDeps(iwBase + 32); }
     }
     const uint32_t off = i - iwBase;
-    if (FUSED) curItemDep = __shfl_sync(0xffffffffu, id0, off);
+    if (FUSED || SHARDED) curItemDep = __shfl_sync(0xffffffffu, id0, off);
     DevItem d;
     d.outAddr = __shfl_sync(0xffffffffu, iw0.x, off);
     d.tileBegin = __shfl_sync(0xffffffffu, iw0.y, off);
@@ -337,6 +391,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   // already left.  Measured A/B: 0.175 -> 0.165 ms per apply at N = 16 384, 0.630 -> 0.608 at 65 536, but
   // 10.67 -> 10.85 ms at N = 524 288 — hence the size switch.
   pdlSync();
+  shardWait();
 #pragma unroll 1
   for (int s = 0; s < kGemvSlots; ++s)
     if (!produce(false)) break;
@@ -452,6 +507,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       T *dst = reinterpret_cast<T *>(a.base[sp] + row * a.ld[sp] * ES);
       if (it.flags & kItemAccumulate) out = S::add(out, FUSED ? __ldcg(dst) : *dst);
       *dst = out;
+      if (SHARDED) { // the ranks that read these rows get them straight into their workspace (same row address)
+        for (uint32_t m = (uint32_t)curItemDep; m; m &= m - 1) {
+          const int r = __ffs(m) - 1;
+          *reinterpret_cast<T *>(a.shard->peerW[r] + row * ES) = out;
+        }
+      }
     }
     if (FUSED && (uint32_t)curItemDep != kNoCounter) { // signal: the rows are complete as far as this stage goes
       __syncwarp(); // the stores of all lanes are ordered before whatever lane 0 does next
@@ -463,6 +524,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     }
   }
   if (FUSED) flushSignal();
+  shardDone();
 }
 
 // ---- many-RHS stage kernel ------------------------------------------------------------------------
@@ -944,13 +1006,17 @@ cudaError_t launchFillSynthetic(int dtype, unsigned char *pool, const FillPiece 
 // ---- launchers ----------------------------------------------------------------------------------------
 cudaError_t configureKernels() {
   cudaError_t e;
-  e = cudaFuncSetAttribute(bfGemvStage<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(bfGemvStage<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(bfGemvStage<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(bfGemvStage<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  e = cudaFuncSetAttribute(bfGemvStage<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfGemvStage<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bfGemvStage<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(bfWideMmaStage<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaSmemBytes);
   if (e != cudaSuccess) return e;
@@ -972,7 +1038,26 @@ cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int /*numSMs*/, cud
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = a.pdl ? 1 : 0;
-  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, false>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, false>, a);
+  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, 0>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, 0>, a);
+}
+
+// One stage of one rank of a block-row sharded operator.  The "last warp posts the flags" count completes when all
+// warps of the grid have finished; no warp waits on anything of its OWN grid or of a LATER stage (only on peers'
+// previous stage), so CTAs need not be co-resident.
+cudaError_t launchGemvShardStage(int dtype, const StageLaunch &a, cudaStream_t stream) {
+  const int ctas = (a.numQueues + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (ctas == 0) return cudaSuccess;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas);
+  cfg.blockDim = dim3(kWarpsPerCta * 32);
+  cfg.dynamicSmemBytes = kGemvSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = a.pdl ? 1 : 0;
+  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, 2>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, 2>, a);
 }
 
 // The whole 1-RHS apply as one cooperative launch (all CTAs co-resident: the readiness spins rely on it).
@@ -989,7 +1074,7 @@ cudaError_t launchGemvFused(int dtype, const StageLaunch &a, cudaStream_t stream
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, true>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, true>, a);
+  return dtype == BF_CUDA_COMPLEX_F64 ? cudaLaunchKernelEx(&cfg, bfGemvStage<true, 1>, a) : cudaLaunchKernelEx(&cfg, bfGemvStage<false, 1>, a);
 }
 
 template <bool CPLX, int CT>

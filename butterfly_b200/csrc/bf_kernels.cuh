@@ -29,6 +29,25 @@ struct StageLaunch {
   const TileDep *tileDeps;
   uint32_t *cnt, *cntNext;
   uint32_t numCounters;
+  // block-row shard (one rank of a sharded operator; bf_comm.cu fills these, see ShardLaunch)
+  const struct ShardLaunch *shard; // device copy, NULL for unsharded plans
+  const uint32_t *itemPeers;       // per item of this stage: ranks that read its rows
+  int stage;
+  uint32_t epoch;                  // apply counter, >= 1
+};
+
+// What a stage kernel of a block-row shard needs to hand rows to its peers: it stores the rows another rank reads
+// straight into that rank's workspace (peer memory over NVLink), and the LAST warp of the grid to finish posts one
+// flag per peer — flags[stage][this rank] = epoch in the peer's flag array; the peer's next stage spins on it.  No
+// collective, no host round trip: all stages of all ranks are enqueued at once.
+constexpr int kMaxRanks = 16;
+struct ShardLaunch {
+  unsigned char *peerW[kMaxRanks];  // workspace base of every rank (entry `rank`: my own)
+  uint32_t *peerFlags[kMaxRanks];   // flag array of every rank: [numStages][world]
+  uint32_t *done;                   // [numStages] warps of my grid that finished stage s (monotonic over applies)
+  uint32_t recvMask[32];            // per stage: ranks that push rows to me during that stage
+  int world, rank, numStages;
+  uint32_t totalWarps;              // warps per stage grid
 };
 
 // Shared-memory geometry of the 1-RHS kernel (one ring of kGemvSlots slots per warp).
@@ -50,6 +69,8 @@ constexpr int kMmaSmemBytes = kMmaRingBytes + kMmaBars * (8 + 8 + 16) + 64;
 
 // 1 RHS: y = A x, one warp per queue, TMA-staged tiles, shuffle reductions.
 cudaError_t launchGemvStage(int dtype, const StageLaunch &a, int numSMs, cudaStream_t stream);
+// 1 RHS, one stage of a block-row shard (a.shard != NULL): peer stores + flags.
+cudaError_t launchGemvShardStage(int dtype, const StageLaunch &a, cudaStream_t stream);
 // 1 RHS, all stages in one cooperative launch (`a` carries the fused tables and the counters).
 cudaError_t launchGemvFused(int dtype, const StageLaunch &a, cudaStream_t stream);
 // nrhs >= 2: one CTA per kWarpsPerCta queues, columns across threads.

@@ -171,10 +171,17 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
   if (desc.bufRows[BF_CUDA_BUF_X] != desc.numCols || desc.bufRows[BF_CUDA_BUF_Y] != desc.numRows) {
     err = "buffer 0 / 1 must have numCols / numRows rows"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
   }
+  const bool sharded = desc.shardWorld > 1;
+  if (sharded && (desc.shardRank < 0 || desc.shardRank >= desc.shardWorld || desc.shardWorld > 16)) {
+    err = "shardRank / shardWorld out of range"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  }
+  if (sharded && rev) { err = "block-row shards are forward only"; return BF_CUDA_ERROR_NOT_IMPLEMENTED; }
   D = Direction();
   D.op = op;
   D.dtype = desc.dtype;
   D.numQueues = numQueues;
+  D.shardWorld = sharded ? desc.shardWorld : 0;
+  D.shardRank = sharded ? desc.shardRank : 0;
   D.inBufId = rev ? BF_CUDA_BUF_Y : BF_CUDA_BUF_X;
   D.outBufId = rev ? BF_CUDA_BUF_X : BF_CUDA_BUF_Y;
   D.rowsIn = desc.bufRows[D.inBufId];
@@ -198,6 +205,10 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     DirOp d{};
     d.kind = o.kind;
     d.remote = (o.flags & BF_CUDA_LEAF_REMOTE) ? 1 : 0;
+    d.owner = (uint8_t)(sharded ? BF_CUDA_LEAF_OWNER(o.flags) : 0);
+    if (sharded && ((int)d.owner >= desc.shardWorld || (d.remote != 0) != ((int)d.owner != desc.shardRank))) {
+      err = "op " + std::to_string(ri) + ": owner bits and REMOTE flag disagree"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
+    }
     d.rawIndex = ri;
     d.val = o.val;
     d.ld = o.ld;
@@ -268,13 +279,21 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
       }
     }
     int64_t arena[2] = {0, 0};
-    for (int32_t s = 0; s < numStages + 2; ++s) arena[s & 1] = std::max(arena[s & 1], perStage[s]);
-    for (int64_t b = 0; b < nB; ++b) {
-      if (cls[b] == 0) D.wsOffset[b] = off[b];
-      else if (cls[b] == 1) D.wsOffset[b] = arena[0] + off[b];
-      else if (cls[b] == 2) D.wsOffset[b] = arena[0] + arena[1] + off[b];
+    if (sharded) {
+      // peers store into this workspace while it is being read: every buffer keeps rows of its own
+      int64_t flat = 0;
+      for (int64_t b = 0; b < nB; ++b)
+        if (cls[b] >= 0) { D.wsOffset[b] = flat; flat += (desc.bufRows[b] + 1) & ~int64_t(1); }
+      D.wsRows = flat;
+    } else {
+      for (int32_t s = 0; s < numStages + 2; ++s) arena[s & 1] = std::max(arena[s & 1], perStage[s]);
+      for (int64_t b = 0; b < nB; ++b) {
+        if (cls[b] == 0) D.wsOffset[b] = off[b];
+        else if (cls[b] == 1) D.wsOffset[b] = arena[0] + off[b];
+        else if (cls[b] == 2) D.wsOffset[b] = arena[0] + arena[1] + off[b];
+      }
+      D.wsRows = arena[0] + arena[1] + dedicated;
     }
-    D.wsRows = arena[0] + arena[1] + dedicated;
     D.wsArena[0] = arena[0]; D.wsArena[1] = arena[1];
     if (D.wsRows > (int64_t)kRowMask || D.rowsIn > (int64_t)kRowMask || D.rowsOut > (int64_t)kRowMask) {
       err = "operator too large for 30-bit row addresses"; return BF_CUDA_ERROR_NOT_IMPLEMENTED;
@@ -482,6 +501,39 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
 
   // ---- 7. fused (single-launch) tables: queue-major, flat workspace, readiness counters ------------
   buildFused(desc, D, firstW, lastW);
+
+  // ---- 8. block-row shards: which of my rows which peer reads ---------------------------------------
+  if (sharded) {
+    const uint32_t me = 1u << desc.shardRank;
+    std::vector<uint16_t> readers((size_t)D.wsRows + 1, 0); // per workspace row: ranks whose leaves read it
+    for (const DirOp &d : D.ops)
+      if (d.inBuf != D.inBufId) {
+        uint16_t *r = readers.data() + D.wsOffset[(size_t)d.inBuf] + d.inOff;
+        for (int64_t i = 0; i < d.k; ++i) r[i] |= (uint16_t)(1u << d.owner);
+      }
+    for (size_t s = 0; s < D.stages.size(); ++s) {
+      Stage &S = D.stages[s];
+      S.itemPeers.assign(S.items.size(), 0u);
+      for (size_t i = 0; i < S.items.size(); ++i) {
+        const DevItem &it = S.items[i];
+        if ((it.outAddr >> 30) != kSpaceW) continue;
+        uint32_t m = 0;
+        const uint16_t *r = readers.data() + (it.outAddr & kRowMask);
+        for (int q = 0; q < it.rows; ++q) m |= r[q];
+        m &= ~me;
+        S.itemPeers[i] = m;
+        S.sendMask |= m;
+        for (uint32_t b = m; b; b &= b - 1) S.sentRows += it.rows;
+      }
+    }
+    for (const DirOp &d : D.ops)
+      if (d.remote && d.outBuf != D.outBufId) {
+        const uint16_t *r = readers.data() + D.wsOffset[(size_t)d.outBuf] + d.outOff;
+        bool mine = false;
+        for (int64_t i = 0; i < d.m && !mine; ++i) mine = (r[i] & me) != 0;
+        if (mine) D.stages[(size_t)d.stage].recvMask |= 1u << d.owner;
+      }
+  }
   return BF_CUDA_OK;
 }
 

@@ -105,6 +105,7 @@ struct DirOp {
   uint8_t swapRC;    // D(p,q) = stored(q,p) instead of stored(p,q)
   uint8_t conj;      // D takes the complex conjugate of the stored value
   uint8_t remote;    // BF_CUDA_LEAF_REMOTE: part of the structure, applied by another rank
+  uint8_t owner;     // sharded descriptors: the rank that applies the leaf
   int64_t rawIndex;  // index in the BfCudaPlanDesc op list (synthetic values hash on this)
   int64_t inBuf, inOff, outBuf, outOff, m, k;
   int64_t ld;        // stored row stride (elements)
@@ -124,6 +125,12 @@ struct Stage {
   std::vector<int64_t> itemBuf, itemElem; // per item: buffer written, elementary interval (host only; fused tables)
   std::vector<int64_t> itemRow;       // per item: first row inside that buffer
   std::vector<int64_t> tileBuf, tileRow; // per tile: buffer read and first row read (-1 for jump tiles)
+  // block-row shards (desc.shardWorld > 1): bit r of itemPeers[i] = rank r reads rows of item i, so the stage
+  // kernel stores them into r's workspace too; sendMask / recvMask = ranks this stage pushes rows to / is
+  // pushed rows by; sentRows = workspace rows pushed (a row pushed to two ranks counts twice)
+  std::vector<uint32_t> itemPeers;
+  uint32_t sendMask = 0, recvMask = 0;
+  int64_t sentRows = 0;
   uint64_t poolBegin16 = 0, poolEnd16 = 0;
   int64_t entries = 0;                // dense entries applied in this stage
 };
@@ -143,6 +150,8 @@ struct Direction {
   int64_t entries = 0;
   int64_t numItems = 0, numTiles = 0, maxTileK = 0, maxItemRows = 0;
   FusedTables fused;
+  int shardWorld = 0, shardRank = 0;  // > 1: one rank's share; the workspace is then flat (no row is reused inside
+                                      // an apply: peers push into it at their own pace)
 };
 
 // Tiling helpers (the kernels static_assert against the same numbers).

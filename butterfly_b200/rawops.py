@@ -43,7 +43,7 @@ class RawOps:
         d = self.ops[self.ops["kind"] == capi.LEAF_DENSE]
         return int((d["m"] * d["k"]).sum())
 
-    def desc(self, device=-1, build_transpose=False) -> capi.PlanDesc:
+    def desc(self, device=-1, build_transpose=False, shard=None) -> capi.PlanDesc:
         """A ctypes BfCudaPlanDesc whose pointers stay valid while `self` is alive."""
         ops = self.ops.copy()
         if self.values is not None:
@@ -64,6 +64,8 @@ class RawOps:
         d.ops = ops.ctypes.data_as(C.POINTER(capi.RawOp))
         d.device = device
         d.buildTranspose = int(build_transpose)
+        if shard is not None:  # (world, rank): one rank's share of a block-row sharded operator
+            d.shardWorld, d.shardRank = int(shard[0]), int(shard[1])
         self._keep = ops  # the pointer table handed to C
         return d
 

@@ -49,7 +49,7 @@
 extern "C" {
 #endif
 
-#define BF_CUDA_ABI_VERSION 1
+#define BF_CUDA_ABI_VERSION 2
 
 typedef enum BfCudaStatus {
   BF_CUDA_OK = 0,
@@ -90,6 +90,11 @@ typedef enum BfCudaLeafKind {
  * another rank applies it: no items, tiles or pool bytes are generated for it here, and the rows it
  * writes are expected to arrive through the caller's exchange (bfCudaApplyStages). */
 #define BF_CUDA_LEAF_REMOTE 8u
+/* Sharded descriptors: bits 8..15 of `flags` hold the rank that applies the leaf (of a REMOTE leaf: which other
+ * rank; of a local one: this rank).  The plan compiler derives from them which rows a stage kernel also stores
+ * into which peer's workspace (BfCudaPlanDesc.shardWorld > 1). */
+#define BF_CUDA_LEAF_OWNER_SHIFT 8
+#define BF_CUDA_LEAF_OWNER(flags) (((flags) >> BF_CUDA_LEAF_OWNER_SHIFT) & 0xFFu)
 
 enum { BF_CUDA_BUF_X = 0, BF_CUDA_BUF_Y = 1, BF_CUDA_BUF_FIRST_TEMP = 2 };
 
@@ -121,6 +126,10 @@ typedef struct BfCudaPlanDesc {
   int32_t device;         /* CUDA device ordinal, -1 = current device */
   int32_t buildTranspose; /* bit 0: also compile A^T (OP_T); bit 1: also compile A^H (OP_H,
                              complex only).  Each extra direction holds its own packed pool. */
+  int32_t shardWorld;     /* 0 / 1: the whole operator on one device.  > 1: one rank's share of a block-row
+                             sharded operator (bfCudaShardDesc builds these): leaves of other ranks carry
+                             BF_CUDA_LEAF_REMOTE, every leaf its owner (BF_CUDA_LEAF_OWNER); forward only */
+  int32_t shardRank;      /* this rank, 0 <= shardRank < shardWorld */
 } BfCudaPlanDesc;
 
 typedef struct BfCudaPlan BfCudaPlan; /* opaque */
@@ -206,6 +215,94 @@ BfCudaStatus bfCudaApplyStages(BfCudaPlan *plan, int32_t op, const void *d_x, in
 BfCudaStatus bfCudaPlanGetWorkspace(BfCudaPlan *plan, int32_t op, int64_t nrhs, void **d_ws, int64_t *ld);
 BfCudaStatus bfCudaPlanGetWorkspaceLayout(const BfCudaPlan *plan, int32_t op, int64_t *arena0Rows,
                                           int64_t *arena1Rows, int64_t *dedicatedRows);
+
+/* ---- one operator over several GPUs -------------------------------------------------------
+ * The reference is single-process, single-thread C; its callers loop over bfMatMul (src/linalg.c:125,155;
+ * examples/multiple_scattering/multiple_scattering_context.c:776-794).  Nothing in it shards an operator, so
+ * these entry points replace no reference interface: they put several GPUs behind the SAME calls.
+ *
+ * Block rows.  bfCudaShardDescsCreate decides which rank applies which leaf (contiguous row ranges of Y and of
+ * every intermediate level; leaves taller than 2048 rows and diagonal terms are cut at the boundaries) and
+ * returns one descriptor per rank: the same leaves everywhere, those of other ranks flagged
+ * BF_CUDA_LEAF_REMOTE.  bfCudaShardDescsGetLayout: yCuts[world + 1] (rank r owns rows [yCuts[r], yCuts[r+1]) of
+ * the result), and per leaf of the sharded list its owner and where it comes from in the original list
+ * (originOp, originRow: per-leaf side data such as Helmholtz recipes follows the cuts through these).  Any of
+ * the output pointers may be NULL. */
+typedef struct BfCudaShardDescs BfCudaShardDescs;
+BfCudaStatus bfCudaShardDescsCreate(const BfCudaPlanDesc *desc, int32_t world, const double *fractions,
+                                    BfCudaShardDescs **out);
+const BfCudaPlanDesc *bfCudaShardDescsGet(const BfCudaShardDescs *descs, int32_t rank);
+BfCudaStatus bfCudaShardDescsGetLayout(const BfCudaShardDescs *descs, int64_t *numOps, int64_t *yCuts,
+                                       int32_t *owner, int64_t *originOp, int64_t *originRow);
+void bfCudaShardDescsFree(BfCudaShardDescs *descs);
+
+/* One rank at run time: its plan (bfCudaShardRankGetPlan: fill its values with bfCudaPlanBuildHelm2 /
+ * bfCudaPlanFillSynthetic, or let the descriptor carry host values), a workspace and a flag array its peers can
+ * store into.  The stage kernels write the rows another rank reads straight into that rank's workspace (peer
+ * memory over NVLink) and post one flag per (stage, peer); the reader's next stage spins on the flag.  There is no
+ * collective and no host round trip between stages.  Set-up: every rank exports a BfCudaShardHandle, the caller
+ * moves the handles between ranks (memcpy in one process; an all_gather of sizeof(BfCudaShardHandle) bytes
+ * between processes) and every rank connects to all of them: same process = the raw pointers (peer access is
+ * enabled), another process = the CUDA IPC handles.  One column per apply. */
+typedef struct BfCudaShardRank BfCudaShardRank;
+typedef struct BfCudaShardHandle {
+  int64_t pid;            /* process that owns the memory */
+  int32_t device, rank;
+  int64_t wsBytes;
+  void *wsPtr, *flagsPtr; /* valid in the owning process only */
+  int32_t hasIpc, reserved;
+  unsigned char wsIpc[64], flagsIpc[64]; /* cudaIpcMemHandle_t */
+} BfCudaShardHandle;
+BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, BfCudaShardRank **out);
+BfCudaStatus bfCudaShardRankDestroy(BfCudaShardRank *rank);
+BfCudaPlan *bfCudaShardRankGetPlan(BfCudaShardRank *rank);
+int64_t bfCudaShardRankSentRows(const BfCudaShardRank *rank); /* workspace rows pushed to peers per apply */
+BfCudaStatus bfCudaShardRankGetHandle(BfCudaShardRank *rank, BfCudaShardHandle *handle);
+BfCudaStatus bfCudaShardRankConnect(BfCudaShardRank *rank, const BfCudaShardHandle *allRanks);
+/* d_x: the FULL operand (numCols elements, dense, 16-byte aligned) on this rank's device; d_y: numRows
+ * elements, of which this rank writes the rows it owns.  Asynchronous.  ...Stages runs stages [stageBegin,
+ * stageEnd) (stageEnd < 0: to the end); stageBegin == 0 starts a new apply.  A driver of several ranks in one
+ * thread launches stage-major so that no device starts late. */
+BfCudaStatus bfCudaShardRankApplyDevice(BfCudaShardRank *rank, const void *d_x, void *d_y, void *stream);
+BfCudaStatus bfCudaShardRankApplyStages(BfCudaShardRank *rank, const void *d_x, void *d_y, int64_t stageBegin,
+                                        int64_t stageEnd, void *stream);
+
+/* All ranks in ONE process, driven by one host thread: what a reference program uses (bfCudaMatAttachSharded in
+ * bf_cuda_attach.h puts it behind bfMatMul).  bfCudaCommInit: the devices to use (NULL: 0 .. nGpus - 1; an
+ * ordinal may repeat — ranks sharing a GPU run one after the other, which is how the single-GPU test exercises
+ * the protocol); one stream per rank.  bfCudaPlanShard: BF_CUDA_SHARD_BLOCK_ROWS as above (forward only, one
+ * column at a time: a block of columns is applied column by column); BF_CUDA_SHARD_RHS_COLS replicates the plan
+ * (desc->buildTranspose honoured) and gives every device a slice of the columns — the mode for wide blocks. */
+typedef struct BfCudaComm BfCudaComm;
+typedef struct BfCudaShardedPlan BfCudaShardedPlan;
+typedef enum BfCudaShardMode { BF_CUDA_SHARD_RHS_COLS = 0, BF_CUDA_SHARD_BLOCK_ROWS = 1 } BfCudaShardMode;
+typedef struct BfCudaShardedInfo {
+  int32_t world, mode;
+  int64_t numRows, numCols;
+  int64_t numEntries;           /* E of the whole operator */
+  int64_t maxRankEntries;       /* largest per-rank share (block rows) */
+  int64_t poolBytesMax;         /* largest per-device factor pool */
+  int64_t sentRowsPerApply;     /* workspace rows pushed between GPUs per apply, all ranks (block rows) */
+  int64_t numStages;
+  int64_t yCuts[17];            /* block rows: row ranges of the result */
+} BfCudaShardedInfo;
+BfCudaStatus bfCudaCommInit(int32_t nGpus, const int32_t *devices, BfCudaComm **comm);
+BfCudaStatus bfCudaCommDestroy(BfCudaComm *comm);
+int32_t bfCudaCommSize(const BfCudaComm *comm);
+BfCudaStatus bfCudaPlanShard(const BfCudaPlanDesc *desc, BfCudaComm *comm, int32_t mode, const double *fractions,
+                             BfCudaShardedPlan **plan);
+BfCudaStatus bfCudaShardedPlanDestroy(BfCudaShardedPlan *plan);
+BfCudaStatus bfCudaShardedPlanGetInfo(const BfCudaShardedPlan *plan, BfCudaShardedInfo *info);
+BfCudaPlan *bfCudaShardedPlanGetRankPlan(BfCudaShardedPlan *plan, int32_t rank);
+/* Host buffers, synchronous: X to every device that needs it, apply, the result rows / columns back. */
+BfCudaStatus bfCudaShardedApplyHost(BfCudaShardedPlan *plan, int32_t op, const void *x, int64_t ldx, int64_t nrhs,
+                                    void *y, int64_t ldy);
+/* Block rows, device resident (the timed entry point): d_x[r] = the full operand on rank r's device, d_y[r] =
+ * numRows elements there (rank r writes its own rows).  Asynchronous on the ranks' streams;
+ * bfCudaShardedSynchronize waits for all of them.  bfCudaShardedRankStream: rank r's stream (cudaStream_t). */
+BfCudaStatus bfCudaShardedApplyDevice(BfCudaShardedPlan *plan, const void *const *d_x, void *const *d_y);
+BfCudaStatus bfCudaShardedSynchronize(BfCudaShardedPlan *plan);
+void *bfCudaShardedRankStream(BfCudaShardedPlan *plan, int32_t rank);
 
 /* Host-buffer apply: H2D of X, apply, D2H of Y, synchronous.  x / y are ordinary host memory
  * (the reference's malloc'ed BfMatDenseComplex::data / BfVecReal::data). */

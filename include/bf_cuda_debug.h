@@ -46,6 +46,12 @@ typedef struct BfCudaDebugTables {
   const void *fusedTileDeps;     /* fusedNumTiles x {u32 counter, u32 total} */
   const uint32_t *fusedQItemBegin; /* [numQueues + 1] */
   const uint32_t *fusedQTileBegin; /* [numQueues + 1] */
+  /* block-row shards (desc->shardWorld > 1), NULL otherwise: per item (parallel to `items`) the ranks that read
+   * its rows — the stage kernel stores them into those ranks' workspaces too — and per stage the ranks that push
+   * rows to this one / that this one pushes rows to */
+  const uint32_t *itemPeers;
+  const uint32_t *stageRecvMask; /* [numStages] */
+  const uint32_t *stageSendMask; /* [numStages] */
 } BfCudaDebugTables;
 
 BfCudaStatus bfCudaDebugCompile(const BfCudaPlanDesc *desc, int32_t op, int32_t numQueues,

@@ -10,10 +10,10 @@ from butterfly_b200 import capi
 
 
 class Tables:
-    def __init__(self, raw, op=capi.OP_N, num_queues=148 * 8):
+    def __init__(self, raw, op=capi.OP_N, num_queues=148 * 8, shard=None):
         self.lib = capi.load_library()
         self.raw = raw
-        self._desc = raw.desc()
+        self._desc = raw.desc(shard=shard)
         t = C.POINTER(capi.DebugTables)()
         capi.check(self.lib.bfCudaDebugCompile(C.byref(self._desc), op, num_queues, C.byref(t)), "bfCudaDebugCompile")
         self._t = t
@@ -35,6 +35,9 @@ class Tables:
         self.rows_in, self.rows_out, self.ws_rows = d.rowsIn, d.rowsOut, d.wsRows
         self.cplx = d.dtype == capi.COMPLEX_F64
         self.ws_arena = (int(d.wsArena0Rows), int(d.wsArena1Rows))
+        self.item_peers = arr(d.itemPeers, d.numItems, np.uint32) if d.itemPeers else None
+        self.recv_mask = arr(d.stageRecvMask, nS, np.uint32) if d.stageRecvMask else None
+        self.send_mask = arr(d.stageSendMask, nS, np.uint32) if d.stageSendMask else None
         self.fused = bool(d.fusedEnabled)
         if self.fused:
             self.f_items = arr(d.fusedItems, d.fusedNumItems, capi.ITEM_DTYPE)
