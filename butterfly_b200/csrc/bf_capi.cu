@@ -318,7 +318,9 @@ static BfCudaStatus applyImpl(BfCudaPlan *P, int32_t op, const void *d_x, int64_
   // the budget: what the device has free (plus what the plan already holds for this purpose) minus a margin,
   // so a 256-column block runs as ONE chunk whenever the memory is there — every extra chunk re-reads the pool
   size_t budget = P->maxScratchBytes;
-  if ((rowsPad + xRowsPad) * (size_t)nrhs * es > P->scratchBytes) {
+  // (only when a block of columns does not fit what the plan already holds: cudaMemGetInfo stalls while the GPU is
+  // busy, it must not sit on the path of a 1-column apply)
+  if (nrhs > 1 && (rowsPad + xRowsPad) * (size_t)nrhs * es > P->scratchBytes) {
     size_t freeB = 0, totalB = 0;
     if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
       const size_t margin = size_t(2) << 30;

@@ -173,7 +173,30 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     for (int s = 0; s < kGemvSlots; ++s) mbarInit(smemU32(&bars[s]), 1);
     fenceBarrierInit();
   }
+  if (SHARDED && threadIdx.x == 0) {
+    // Block-row shard: the rows peers pushed during the previous stage have landed once their flags show this
+    // apply's epoch (a flag is written after the rows).  Stage 0 instead waits for EVERY peer to have finished the
+    // previous apply (their last stage's flag, epoch - 1): its workspace rows are about to be overwritten.
+    // ONE thread per CTA polls, with relaxed loads and a single fence at the end; the CTA barrier below hands the
+    // result to the other warps.  (Every warp polling with ld.acquire.sys — 1 776 pollers on one line — cost
+    // 0.4 - 1 ms per apply at N = 524 288.)  Every CTA waits, also one without work: the NEXT stage relies on this
+    // grid having seen the previous pushes.
+    const ShardLaunch &sh = *a.shard;
+    const int ws = a.stage == 0 ? sh.numStages - 1 : a.stage - 1;
+    const uint32_t want = a.stage == 0 ? a.epoch - 1u : a.epoch;
+    uint32_t mask = a.stage == 0 ? ((1u << sh.world) - 1u) & ~(1u << sh.rank) : sh.recvMask[ws];
+    const volatile uint32_t *flags = sh.peerFlags[sh.rank] + (size_t)ws * sh.world;
+    for (; mask; mask &= mask - 1) {
+      const int r = __ffs(mask) - 1;
+      for (unsigned long long spins = 0; (int32_t)(flags[r] - want) < 0; ++spins) {
+        if (spins > (1ull << 25)) __trap(); // a peer that never arrives: fail loudly instead of hanging
+        __nanosleep(100);
+      }
+    }
+    __threadfence_system(); // acquire: the rows behind the flags
+  }
   __syncthreads();
+  if (SHARDED && lane == 0) fenceProxyAsyncGlobal(); // peer stores (generic proxy) -> this lane's bulk copies
 
   // Under programmatic dependent launch EVERY exit path runs griddepcontrol.wait first: stage-to-stage
   // ordering is transitive only through grids whose threads all waited, and a stage with no local items
@@ -189,30 +212,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.numCounters; i += gridDim.x * blockDim.x) a.cntNext[i] = 0u;
   }
   // block-row shard: hand-over between ranks
-  auto shardWait = [&]() { // rows pushed by peers during the previous stage have landed (flags are written after them)
-    if (!SHARDED) return;
-    const ShardLaunch &sh = *a.shard;
-    if (lane == 0) {
-      // stage 0 waits for EVERY peer to have finished the previous apply (their last stage's flag, epoch - 1)
-      const int ws = a.stage == 0 ? sh.numStages - 1 : a.stage - 1;
-      const uint32_t want = a.stage == 0 ? a.epoch - 1u : a.epoch;
-      uint32_t mask = a.stage == 0 ? ((1u << sh.world) - 1u) & ~(1u << sh.rank) : sh.recvMask[ws];
-      const uint32_t *flags = sh.peerFlags[sh.rank] + (size_t)ws * sh.world;
-      for (; mask; mask &= mask - 1) {
-        const int r = __ffs(mask) - 1;
-        unsigned long long spins = 0;
-        uint32_t v;
-        do {
-          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
-          if ((int32_t)(v - want) >= 0) break;
-          if (++spins > (1ull << 26)) __trap(); // a peer that never arrives: fail loudly instead of hanging
-          __nanosleep(64);
-        } while (true);
-      }
-      fenceProxyAsyncGlobal(); // peer stores (generic proxy, another GPU) -> this thread's bulk copies
-    }
-    __syncwarp();
-  };
   auto shardDone = [&]() { // this warp's stores (local and to peers) are complete; the last warp posts the flags
     if (!SHARDED) return;
     __syncwarp();
@@ -230,11 +229,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       }
     }
   };
-  // (every warp waits, also one without work: the NEXT stage relies on this grid having seen the previous pushes)
-  if (q >= a.numQueues) { pdlSync(); shardWait(); shardDone(); return; }
+  if (q >= a.numQueues) { pdlSync(); shardDone(); return; }
   const uint32_t iBeg = a.qItemBegin[q], iEnd = a.qItemBegin[q + 1];
   const uint32_t tBeg = a.qTileBegin[q], tEnd = a.qTileBegin[q + 1];
-  if (iBeg == iEnd) { pdlSync(); shardWait(); shardDone(); return; }
+  if (iBeg == iEnd) { pdlSync(); shardDone(); return; }
   const uint64_t pol = policyEvictFirst();
 
   // Descriptor windows: lane l holds tiles[twBase + l] / tiles[twBase + 32 + l] (and the same for
@@ -391,7 +389,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
   // already left.  Measured A/B: 0.175 -> 0.165 ms per apply at N = 16 384, 0.630 -> 0.608 at 65 536, but
   // 10.67 -> 10.85 ms at N = 524 288 — hence the size switch.
   pdlSync();
-  shardWait();
 #pragma unroll 1
   for (int s = 0; s < kGemvSlots; ++s)
     if (!produce(false)) break;
