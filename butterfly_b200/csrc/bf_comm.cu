@@ -156,6 +156,7 @@ extern "C" BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, Bf
   h.totalWarps = (uint32_t)((D.numQueues + kWarpsPerCta - 1) / kWarpsPerCta) * (uint32_t)kWarpsPerCta;
   for (int s = 0; s < R->numStages; ++s) {
     h.recvMask[s] = D.stages[(size_t)s].recvMask;
+    h.sendMask[s] = D.stages[(size_t)s].sendMask;
     R->sentRows += D.stages[(size_t)s].sentRows;
   }
   *out = R.release();

@@ -212,20 +212,29 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.numCounters; i += gridDim.x * blockDim.x) a.cntNext[i] = 0u;
   }
   // block-row shard: hand-over between ranks
+  bool pushedToPeers = false; // this warp stored rows into another rank's workspace
   auto shardDone = [&]() { // this warp's stores (local and to peers) are complete; the last warp posts the flags
     if (!SHARDED) return;
     __syncwarp();
     if (lane == 0) {
       const ShardLaunch &sh = *a.shard;
-      __threadfence_system();
+      // Only a warp that stored into a peer needs its stores performed system-wide before it counts itself done
+      // (rows kept on this GPU are handed to the next stage by the kernel boundary).  A system fence in every warp
+      // — 1 776 of them arriving together — cost ~20 us per stage.
+      if (pushedToPeers) __threadfence_system();
+      else __threadfence();
       const uint32_t old = atomicAdd(sh.done + a.stage, 1u);
       if ((old + 1u) % sh.totalWarps == 0u) {
+        // ONE system fence (release: every warp's rows, observed through the counter above), then plain flag
+        // stores — to the ranks that wait on this stage only; after the last stage to everybody (stage 0 of the
+        // next apply waits for all peers).  Seven st.release.sys in a row cost ~15 us per stage.
         __threadfence_system();
-        for (int r = 0; r < sh.world; ++r)
-          if (r != sh.rank) {
-            uint32_t *f = sh.peerFlags[r] + (size_t)a.stage * sh.world + sh.rank;
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.epoch) : "memory");
-          }
+        uint32_t to = a.stage == sh.numStages - 1 ? ((1u << sh.world) - 1u) & ~(1u << sh.rank) : sh.sendMask[a.stage];
+        for (; to; to &= to - 1) {
+          const int r = __ffs(to) - 1;
+          uint32_t *f = sh.peerFlags[r] + (size_t)a.stage * sh.world + sh.rank;
+          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.epoch) : "memory");
+        }
       }
     }
   };
@@ -505,6 +514,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) bfGemvStage(const __grid
       if (it.flags & kItemAccumulate) out = S::add(out, FUSED ? __ldcg(dst) : *dst);
       *dst = out;
       if (SHARDED) { // the ranks that read these rows get them straight into their workspace (same row address)
+        if ((uint32_t)curItemDep) pushedToPeers = true; // (warp-uniform: the mask belongs to the item)
         for (uint32_t m = (uint32_t)curItemDep; m; m &= m - 1) {
           const int r = __ffs(m) - 1;
           *reinterpret_cast<T *>(a.shard->peerW[r] + row * ES) = out;

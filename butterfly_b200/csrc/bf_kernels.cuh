@@ -46,6 +46,7 @@ struct ShardLaunch {
   uint32_t *peerFlags[kMaxRanks];   // flag array of every rank: [numStages][world]
   uint32_t *done;                   // [numStages] warps of my grid that finished stage s (monotonic over applies)
   uint32_t recvMask[32];            // per stage: ranks that push rows to me during that stage
+  uint32_t sendMask[32];            // per stage: ranks I push rows to (they wait for my flag of that stage)
   int world, rank, numStages;
   uint32_t totalWarps;              // warps per stage grid
 };

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <climits>
 #include <complex>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -405,6 +406,8 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
       int64_t rowBytes = 0;
       for (size_t q = f; q < f1; ++q)
         if (D.ops[(size_t)frags[q].seq].kind == BF_CUDA_LEAF_DENSE) rowBytes += D.ops[(size_t)frags[q].seq].k * esBytes;
+      // (not finer than that: cutting down to a quarter of the share evens the queues out on paper, but 8-row items
+      // move 4 KiB tiles and the apply got 10 % SLOWER at N = 65 536 — measured, profiles/r2i_plan_knobs.txt)
       const int64_t share = stageBytes[(size_t)frags[f].stage] / std::max(numQueues, 1);
       while (R > 8 && (int64_t)R * rowBytes > share) R -= 8;
     }
@@ -478,16 +481,60 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     S.qItemBegin.assign((size_t)numQueues + 1, (uint32_t)nI);
     S.qTileBegin.assign((size_t)numQueues + 1, (uint32_t)nT);
     S.qPool16.assign((size_t)numQueues + 1, pool16);
+    // Contiguous partition with the smallest possible bottleneck: the least capacity C for which "fill a queue
+    // until the next item would overflow C" needs at most numQueues queues (binary search), then a pass that stops
+    // a queue early once it holds its share of what is left (even queues instead of full ones followed by empty
+    // ones), falling back to the plain fill if that runs out of queues.  A stage lasts as long as its slowest
+    // queue; the former rule (deal items while their midpoint lies before the queue's share boundary) left some
+    // queues with two share-sized items: slowest / mean queue bytes 1.9 on an 8-way row shard of N = 524 288, now
+    // 1.2 - 1.35; N = 16 384 apply 0.153 -> 0.142 ms, 8-GPU shard 1.86 -> 1.77 ms.
     const uint64_t total = cost[nI];
-    size_t i = 0;
+    std::vector<uint32_t> qEnd((size_t)numQueues, (uint32_t)nI); // items [qEnd[q-1], qEnd[q]) belong to queue q
+    if (nI > 0) {
+      uint64_t lo = 0;
+      for (size_t i = 0; i < nI; ++i) lo = std::max(lo, cost[i + 1] - cost[i]);
+      uint64_t hi = total;
+      lo = std::max(lo, (total + (uint64_t)numQueues - 1) / (uint64_t)numQueues);
+      auto queuesNeeded = [&](uint64_t C) {
+        int used = 1;
+        uint64_t acc = 0;
+        for (size_t i = 0; i < nI; ++i) {
+          const uint64_t c = cost[i + 1] - cost[i];
+          if (acc + c > C && acc > 0) { ++used; acc = 0; }
+          acc += c;
+        }
+        return used;
+      };
+      while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if (queuesNeeded(mid) <= numQueues) hi = mid; else lo = mid + 1;
+      }
+      const uint64_t C = lo;
+      auto fill = [&](bool even) {
+        size_t i = 0;
+        for (int q = 0; q < numQueues; ++q) {
+          const uint64_t left = total - cost[i];
+          const uint64_t fair = (left + (uint64_t)(numQueues - q) - 1) / (uint64_t)(numQueues - q);
+          uint64_t acc = 0;
+          while (i < nI) {
+            const uint64_t c = cost[i + 1] - cost[i];
+            if (acc > 0 && acc + c > C) break;
+            if (even && acc > 0 && acc + c / 2 > fair) break;
+            acc += c;
+            ++i;
+          }
+          qEnd[(size_t)q] = (uint32_t)i;
+        }
+        return i == nI;
+      };
+      if (!fill(true)) fill(false);
+      qEnd[(size_t)numQueues - 1] = (uint32_t)nI;
+    }
     for (int q = 0; q < numQueues; ++q) {
+      const size_t i = q == 0 ? 0 : qEnd[(size_t)q - 1];
       S.qItemBegin[(size_t)q] = (uint32_t)i;
       S.qTileBegin[(size_t)q] = i < nI ? S.items[i].tileBegin : (uint32_t)nT;
       S.qPool16[(size_t)q] = (i < nI && S.items[i].tileBegin < nT) ? S.tilePool16[S.items[i].tileBegin] : pool16;
-      // take items while their midpoint lies before this queue's share boundary
-      const long double bound = (long double)total * (q + 1) / numQueues;
-      while (i < nI && (long double)(cost[i] + cost[i + 1]) * 0.5L < bound) ++i;
-      if (q == numQueues - 1) i = nI;
     }
     // fix pool offsets of queues that begin at an item without tiles: the next tile in order
     for (int q = numQueues - 1; q >= 0; --q) {

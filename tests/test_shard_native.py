@@ -97,6 +97,12 @@ def test_all_ranks_emulated_with_peer_pushes(name, world, fractions):
                             pushed_rows += rows
                     seen |= int(peers)
                 assert seen == int(t.send_mask[s])
+        # the two sides of the hand-over are derived independently (sender: items -> readers; reader: remote leaves):
+        # rank q waits for rank r's flag of stage s exactly when r posts one to q
+        for s in range(nS):
+            for r in range(world):
+                for q in range(world):
+                    assert ((int(tabs[r].send_mask[s]) >> q) & 1) == ((int(tabs[q].recv_mask[s]) >> r) & 1), (s, r, q)
         y = np.full_like(y_ref, np.nan)
         for r in range(world):
             y[cuts[r]:cuts[r + 1]] = spaces[r][1][cuts[r]:cuts[r + 1]]
