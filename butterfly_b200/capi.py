@@ -266,6 +266,8 @@ ATTACH_EXPORTED_SYMBOLS = [
     "bfCudaMatSetPerms",
     "bfCudaSolveGMRESMat",
     "bfCudaMatAttachHelm2",
+    "bfCudaMatAttachSharded",
+    "bfCudaMatGetShardedPlan",
 ]
 # libbfcuda_helm2.so (csrc/bf_helm2_record.c): the recorder of the reference's Helmholtz value builders
 HELM2_EXPORTED_SYMBOLS = [

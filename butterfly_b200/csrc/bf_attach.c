@@ -32,6 +32,9 @@ typedef struct Wrapper {
                            AddInplace ...): re-flatten before the next apply */
   int valueless;        /* attached through a helm2 recording: the leaves hold no host values, so
                            the object cannot be edited or re-flattened */
+  BfCudaShardedPlan *sharded; /* bfCudaMatAttachSharded: the operator lives on several GPUs (plan == NULL then) */
+  BfCudaComm *comm;           /* borrowed; must outlive the attachment */
+  int shardMode;
   int64_t *inPerm, *outPerm; /* host copies of the fused permutations (survive a refresh) */
   int64_t numInPerm, numOutPerm;
 } Wrapper;
@@ -57,6 +60,7 @@ static Wrapper *wrapperOf(BfMat const *A) {
 
 static void freeWrapper(Wrapper *w) {
   bfCudaPlanDestroy(w->plan);
+  bfCudaShardedPlanDestroy(w->sharded);
   w->magic = 0;
   free(w->inPerm);
   free(w->outPerm);
@@ -71,6 +75,21 @@ static int refreshIfDirty(BfMat const *A) {
   BfCudaPlanDesc *desc = NULL;
   BfCudaStatus st = bfCudaFlattenEx(A, w->opts.flattenFlags, &desc);
   BfCudaPlan *plan = NULL;
+  if (st == BF_CUDA_OK && w->comm) { /* several GPUs: re-shard the edited operator */
+    BfCudaShardedPlan *sp = NULL;
+    desc->buildTranspose = w->opts.buildTranspose;
+    st = bfCudaPlanShard(desc, w->comm, w->shardMode, NULL, &sp);
+    bfCudaFlattenFree(desc);
+    if (st != BF_CUDA_OK) {
+      bfSetError(BF_ERROR_RUNTIME_ERROR);
+      return 0;
+    }
+    bfCudaShardedPlanDestroy(w->sharded);
+    w->sharded = sp;
+    w->dirty = 0;
+    w->transposed = 0;
+    return 1;
+  }
   if (st == BF_CUDA_OK) {
     desc->device = w->opts.device;
     desc->buildTranspose = w->opts.buildTranspose;
@@ -94,6 +113,12 @@ static int refreshIfDirty(BfMat const *A) {
 static int forwardOp(Wrapper const *w) {
   if (!w->transposed) return BF_CUDA_OP_N;
   return w->dtype == BF_CUDA_COMPLEX_F64 ? BF_CUDA_OP_H : BF_CUDA_OP_T; /* src/mat_dense_complex.c:1475-1478 */
+}
+
+/* Host-buffer apply on whatever holds the operator: one plan, or a sharded plan over several GPUs. */
+static BfCudaStatus applyHostW(Wrapper *w, int op, const void *x, int64_t ldx, int64_t nrhs, void *y, int64_t ldy) {
+  if (w->sharded) return bfCudaShardedApplyHost(w->sharded, op, x, ldx, nrhs, y, ldy);
+  return applyHostW(w, op, x, ldx, nrhs, y, ldy);
 }
 
 static enum BfError toBfError(BfCudaStatus st) {
@@ -129,7 +154,7 @@ static BfMat *attachedMul(BfMat const *A, BfMat const *X) {
   }
   BfMatDenseComplex *Y = bfMatDenseComplexNew();
   bfMatDenseComplexInit(Y, bfMatGetNumRows(A), nrhs);
-  BfCudaStatus st = bfCudaApplyHost(w->plan, forwardOp(w), Xd->data, (int64_t)Xd->rowStride, (int64_t)nrhs,
+  BfCudaStatus st = applyHostW(w, forwardOp(w), Xd->data, (int64_t)Xd->rowStride, (int64_t)nrhs,
                                     Y->data, (int64_t)Y->rowStride);
   if (st != BF_CUDA_OK) {
     BfMat *Ym = bfMatDenseComplexToMat(Y);
@@ -173,7 +198,7 @@ static BfMat *attachedRmul(BfMat const *A, BfMat const *X) {
       BfComplex v = Xd->data[i * Xd->rowStride + j];
       xt[j * p + i] = cj ? conj(v) : v;
     }
-  BfCudaStatus st = bfCudaApplyHost(w->plan, cj ? BF_CUDA_OP_N : BF_CUDA_OP_T, xt, (int64_t)p, (int64_t)p, yt, (int64_t)p);
+  BfCudaStatus st = applyHostW(w, cj ? BF_CUDA_OP_N : BF_CUDA_OP_T, xt, (int64_t)p, (int64_t)p, yt, (int64_t)p);
   BfMat *result = NULL;
   if (st == BF_CUDA_OK) {
     BfMatDenseComplex *Y = bfMatDenseComplexNew();
@@ -205,7 +230,7 @@ static BfVec *applyVec(BfMat const *A, BfVec const *x, int rmul) {
     int op = (rmul != 0) != (w->transposed != 0) ? BF_CUDA_OP_T : BF_CUDA_OP_N;
     BfVecReal const *xr = bfVecConstToVecRealConst(x);
     BfVecReal *y = bfVecRealNewEmpty(nOut);
-    BfCudaStatus st = bfCudaApplyHost(w->plan, op, xr->data, (int64_t)xr->stride, 1, y->data, (int64_t)y->stride);
+    BfCudaStatus st = applyHostW(w, op, xr->data, (int64_t)xr->stride, 1, y->data, (int64_t)y->stride);
     if (st != BF_CUDA_OK) {
       BfVec *yv = bfVecRealToVec(y);
       bfVecDelete(&yv);
@@ -230,11 +255,11 @@ static BfVec *applyVec(BfMat const *A, BfVec const *x, int rmul) {
     if (cj) {
       tmp = malloc(sizeof(BfComplex) * (nIn ? nIn : 1));
       for (BfSize i = 0; i < nIn; ++i) tmp[i] = conj(xc->data[i * xc->stride]);
-      st = bfCudaApplyHost(w->plan, op, tmp, 1, 1, y->data, (int64_t)y->stride);
+      st = applyHostW(w, op, tmp, 1, 1, y->data, (int64_t)y->stride);
       for (BfSize i = 0; i < nOut; ++i) y->data[i * y->stride] = conj(y->data[i * y->stride]);
       free(tmp);
     } else {
-      st = bfCudaApplyHost(w->plan, op, xc->data, (int64_t)xc->stride, 1, y->data, (int64_t)y->stride);
+      st = applyHostW(w, op, xc->data, (int64_t)xc->stride, 1, y->data, (int64_t)y->stride);
     }
     if (st != BF_CUDA_OK) {
       BfVec *yv = bfVecComplexToVec(y);
@@ -303,7 +328,8 @@ static int beginEdit(BfMat *A) {
 static void attachedTranspose(BfMat *A) {
   Wrapper *w = wrapperOf(A);
   const int need = w->dtype == BF_CUDA_COMPLEX_F64 ? 2 : 1;
-  if (!w->dirty && (w->opts.buildTranspose & need)) {
+  const int hasReverse = (w->opts.buildTranspose & need) && !(w->sharded && w->shardMode == BF_CUDA_SHARD_BLOCK_ROWS);
+  if (!w->dirty && hasReverse) {
     w->transposed ^= 1;
   } else if (!beginEdit(A)) {
     return;
@@ -338,10 +364,11 @@ static int isAttached(BfMat const *A) {
 extern BfCudaStatus bfCudaHelm2Resolve(BfCudaHelm2Recording *, BfCudaPlanDesc *, BfCudaHelm2Build *) __attribute__((weak));
 
 static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHelm2Recording *rec,
-                               BfCudaHelm2Stats *stats) {
+                               BfCudaHelm2Stats *stats, BfCudaComm *comm, int shardMode) {
   if (!A) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   if (isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
   if (rec && !bfCudaHelm2Resolve) return BF_CUDA_ERROR_NOT_IMPLEMENTED;
+  if (rec && comm) return BF_CUDA_ERROR_NOT_IMPLEMENTED; /* (a recorded operator is sharded through bfCudaShardDescs*) */
   BfCudaPlanDesc *desc = NULL;
   BfCudaStatus st = bfCudaFlattenEx(A, opts ? opts->flattenFlags : 0u, &desc);
   if (st != BF_CUDA_OK) return st;
@@ -351,7 +378,8 @@ static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHel
   /* recorded leaves: map them to their recipes and strip the (inaccessible) value pointers */
   if (rec) st = bfCudaHelm2Resolve(rec, desc, &build);
   BfCudaPlan *plan = NULL;
-  if (st == BF_CUDA_OK) st = bfCudaPlanCreate(desc, &plan);
+  BfCudaShardedPlan *sharded = NULL;
+  if (st == BF_CUDA_OK) st = comm ? bfCudaPlanShard(desc, comm, shardMode, NULL, &sharded) : bfCudaPlanCreate(desc, &plan);
   int dtype = desc->dtype;
   bfCudaFlattenFree(desc);
   if (st != BF_CUDA_OK) return st;
@@ -365,11 +393,15 @@ static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHel
   Wrapper *w = calloc(1, sizeof *w);
   if (!w) {
     bfCudaPlanDestroy(plan);
+    bfCudaShardedPlanDestroy(sharded);
     return BF_CUDA_ERROR_OUT_OF_MEMORY;
   }
   w->vt = *A->vtbl;
   w->orig = A->vtbl;
   w->plan = plan;
+  w->sharded = sharded;
+  w->comm = comm;
+  w->shardMode = shardMode;
   w->dtype = dtype;
   w->magic = WRAPPER_MAGIC;
   if (opts) w->opts = *opts;
@@ -407,12 +439,19 @@ static BfCudaStatus attachWith(BfMat *A, BfCudaAttachOpts const *opts, BfCudaHel
   return BF_CUDA_OK;
 }
 
-BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) { return attachWith(A, opts, NULL, NULL); }
+BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts) { return attachWith(A, opts, NULL, NULL, NULL, 0); }
+
+BfCudaStatus bfCudaMatAttachSharded(BfMat *A, BfCudaComm *comm, int32_t mode, BfCudaAttachOpts const *opts) {
+  if (!comm) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  return attachWith(A, opts, NULL, NULL, comm, mode);
+}
+
+BfCudaShardedPlan *bfCudaMatGetShardedPlan(BfMat const *A) { return isAttached(A) ? wrapperOf(A)->sharded : NULL; }
 
 BfCudaStatus bfCudaMatAttachHelm2(BfMat *A, BfCudaHelm2Recording *rec, BfCudaAttachOpts const *opts,
                                   BfCudaHelm2Stats *stats) {
   if (!rec) return BF_CUDA_ERROR_INVALID_ARGUMENT;
-  return attachWith(A, opts, rec, stats);
+  return attachWith(A, opts, rec, stats, NULL, 0);
 }
 
 BfCudaStatus bfCudaMatDetach(BfMat *A) {
@@ -427,6 +466,10 @@ BfCudaStatus bfCudaMatDetach(BfMat *A) {
  * (forward direction = the transposed object) if bfMatTranspose flipped it. */
 static BfCudaPlan *currentForwardPlan(BfMat const *A) {
   Wrapper *w = wrapperOf(A);
+  if (w->sharded) { /* no single plan behind a sharded attachment */
+    bfSetError(BF_ERROR_NOT_IMPLEMENTED);
+    return NULL;
+  }
   if (w->transposed) {
     if (w->valueless) {
       bfSetError(BF_ERROR_NOT_IMPLEMENTED);
@@ -441,6 +484,7 @@ BfCudaPlan *bfCudaMatGetPlan(BfMat const *A) { return isAttached(A) ? currentFor
 
 BfCudaStatus bfCudaMatSetPerms(BfMat *A, BfPerm const *inPerm, BfPerm const *outPerm) {
   if (!isAttached(A)) return BF_CUDA_ERROR_INVALID_ARGUMENT;
+  if (wrapperOf(A)->sharded) return BF_CUDA_ERROR_NOT_IMPLEMENTED;
   int64_t *in = NULL, *out = NULL;
   if (inPerm) {
     in = malloc(sizeof(int64_t) * (inPerm->size ? inPerm->size : 1));

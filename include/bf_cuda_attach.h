@@ -52,6 +52,17 @@ void bfCudaFlattenFree(BfCudaPlanDesc *desc);
 /* Flatten + compile + upload + swap the vtable.  The plan is a snapshot: in-place edits of `A`
  * (bfMatScaleCols, bfMatAddInplace ...) after attaching are not seen; detach, edit, re-attach. */
 BfCudaStatus bfCudaMatAttach(BfMat *A, BfCudaAttachOpts const *opts);
+/* The same with the operator on SEVERAL GPUs of this process (bf_cuda.h: bfCudaCommInit, bfCudaPlanShard): the
+ * reference's callers — bfMatMul in a loop, bfSolveGMRES (src/linalg.c:125,155), the multiple-scattering solve
+ * (examples/multiple_scattering/multiple_scattering_context.c:776-794) — then drive all of them from their one
+ * host thread with no source change.  mode = BF_CUDA_SHARD_BLOCK_ROWS: every GPU stores 1 / nGpus of the factors
+ * (operators larger than one GPU's memory; forward products only: bfMatRmul / bfMatRmulVec raise
+ * BF_ERROR_NOT_IMPLEMENTED, bfMatTranspose re-shards the transposed operator at the next product);
+ * BF_CUDA_SHARD_RHS_COLS: replicas, the columns of X are split (wide blocks; all directions).
+ * `comm` is borrowed and must outlive the attachment.  bfCudaMatGetPlan returns NULL for such an object,
+ * bfCudaMatGetShardedPlan the sharded plan; fused permutations are not supported on it. */
+BfCudaStatus bfCudaMatAttachSharded(BfMat *A, BfCudaComm *comm, int32_t mode, BfCudaAttachOpts const *opts);
+BfCudaShardedPlan *bfCudaMatGetShardedPlan(BfMat const *A);
 /* Restore the original vtable and free the plan.  No-op error if `A` is not attached. */
 BfCudaStatus bfCudaMatDetach(BfMat *A);
 /* The plan behind an attached object (NULL if not attached); borrowed. */

@@ -87,6 +87,8 @@ def load_attach():
         a.bfCudaMatAttach.argtypes = [C.c_void_p, C.POINTER(AttachOpts)]; a.bfCudaMatAttach.restype = C.c_int32
         a.bfCudaMatDetach.argtypes = [C.c_void_p]; a.bfCudaMatDetach.restype = C.c_int32
         a.bfCudaMatGetPlan.argtypes = [C.c_void_p]; a.bfCudaMatGetPlan.restype = C.c_void_p
+        a.bfCudaMatAttachSharded.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(AttachOpts)]; a.bfCudaMatAttachSharded.restype = C.c_int32
+        a.bfCudaMatGetShardedPlan.argtypes = [C.c_void_p]; a.bfCudaMatGetShardedPlan.restype = C.c_void_p
         _att = a
     return _att
 
@@ -258,6 +260,15 @@ class Helm2:
         if st != 0:
             raise capi.BfCudaError(st, "bfCudaMatAttach", capi.load_library().bfCudaLastErrorMessage().decode())
 
+    def attach_sharded(self, comm, mode=capi.SHARD_BLOCK_ROWS, build_transpose=0):
+        """bfCudaMatAttachSharded: the operator over the GPUs of `comm` (butterfly_b200.sharded.Comm), behind the
+        same vtable."""
+        a = load_attach()
+        o = a.AttachOpts(-1, build_transpose, 0)
+        st = a.bfCudaMatAttachSharded(self.mat, comm.handle, mode, C.byref(o))
+        if st != 0:
+            raise capi.BfCudaError(st, "bfCudaMatAttachSharded", capi.load_library().bfCudaLastErrorMessage().decode())
+
     def plan_handle(self):
         """bfCudaMatGetPlan: the plan behind the attached object (borrowed)."""
         h = load_attach().bfCudaMatGetPlan(self.mat)
@@ -400,6 +411,7 @@ class Stream:
     attach = Helm2.attach
     detach = Helm2.detach
     plan_handle = Helm2.plan_handle
+    attach_sharded = Helm2.attach_sharded
 
 
 def sphere_stream(n: int = 4000, lmax: int = 31, tol: float = 1e-3, freq_tree_depth: int = -1) -> "Stream":
