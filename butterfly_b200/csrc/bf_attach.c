@@ -118,7 +118,7 @@ static int forwardOp(Wrapper const *w) {
 /* Host-buffer apply on whatever holds the operator: one plan, or a sharded plan over several GPUs. */
 static BfCudaStatus applyHostW(Wrapper *w, int op, const void *x, int64_t ldx, int64_t nrhs, void *y, int64_t ldy) {
   if (w->sharded) return bfCudaShardedApplyHost(w->sharded, op, x, ldx, nrhs, y, ldy);
-  return applyHostW(w, op, x, ldx, nrhs, y, ldy);
+  return bfCudaApplyHost(w->plan, op, x, ldx, nrhs, y, ldy);
 }
 
 static enum BfError toBfError(BfCudaStatus st) {
