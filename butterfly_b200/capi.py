@@ -248,6 +248,9 @@ EXPORTED_SYMBOLS = [
     "bfCudaPlanGetStageEntries",
     "bfCudaPlanBuildHelm2",
     "bfCudaHelm2Evaluate",
+    "bfCudaPlanSave",
+    "bfCudaPlanLoad",
+    "bfCudaShardRankLoad",
     "bfCudaRawOpsSave",
     "bfCudaRawOpsLoad",
     "bfCudaRawOpsFree",
@@ -333,6 +336,12 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.bfCudaPlanSetProfiling.restype = i32
     lib.bfCudaPlanGetStageTimes.argtypes = [vp, C.POINTER(C.c_float), i64, C.POINTER(i64)]
     lib.bfCudaPlanGetStageTimes.restype = i32
+    lib.bfCudaPlanSave.argtypes = [vp, C.c_char_p]
+    lib.bfCudaPlanSave.restype = i32
+    lib.bfCudaPlanLoad.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
+    lib.bfCudaPlanLoad.restype = i32
+    lib.bfCudaShardRankLoad.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
+    lib.bfCudaShardRankLoad.restype = i32
     lib.bfCudaRawOpsSave.argtypes = [C.POINTER(PlanDesc), C.c_char_p]
     lib.bfCudaRawOpsSave.restype = i32
     lib.bfCudaRawOpsLoad.argtypes = [C.c_char_p, C.POINTER(C.POINTER(PlanDesc))]

@@ -21,7 +21,8 @@ namespace bfc {
 BfCudaStatus fail(BfCudaStatus st, const std::string &msg) { g_lastError = msg; return st; }
 } // namespace bfc
 
-static BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
+namespace bfc {
+BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
   Direction &D = dd.host;
   const size_t nS = D.stages.size();
   const size_t Q = (size_t)D.numQueues;
@@ -98,12 +99,14 @@ static BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
     dd.fusedWsRows = F.wsRows;
     dd.tableBytes += (int64_t)(F.items.size() * 24 + F.tiles.size() * 16 + 2 * (Q + 1) * 4 + 2 * (size_t)F.numCounters * 4);
     dd.fusedReady = true;
+    dd.fNumItems = F.items.size(); dd.fNumTiles = F.tiles.size();
     F.items = {}; F.itemDeps = {}; F.tiles = {}; F.tileDeps = {}; // device-resident now
   }
   (void)P;
   dd.built = true;
   return BF_CUDA_OK;
 }
+} // namespace bfc
 
 extern "C" {
 
@@ -575,6 +578,7 @@ BfCudaStatus bfCudaApplyHost(BfCudaPlan *P, int32_t op, const void *x, int64_t l
 
 BfCudaStatus bfCudaPlanFillSynthetic(BfCudaPlan *P, uint64_t seed) {
   if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  if (P->loadedFromFile) return fail(BF_CUDA_ERROR_NOT_IMPLEMENTED, "a plan loaded from a file holds no per-leaf data: its values cannot be re-filled");
   DeviceGuard g(P->device);
   for (auto &dd : P->dir) {
     if (!dd.built) continue;

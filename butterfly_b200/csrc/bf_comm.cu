@@ -120,12 +120,10 @@ extern "C" BfCudaStatus bfCudaShardRankDestroy(BfCudaShardRank *R) {
   return BF_CUDA_OK;
 }
 
-extern "C" BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, BfCudaShardRank **out) {
-  if (!rankDesc || !out) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
-  *out = nullptr;
+// Takes ownership of `plan` (destroyed on failure too).
+static BfCudaStatus wrapRankPlan(BfCudaPlan *plan, BfCudaShardRank **out) {
   std::unique_ptr<BfCudaShardRank> R(new BfCudaShardRank());
-  BfCudaStatus st = bfCudaPlanCreate(rankDesc, &R->plan);
-  if (st != BF_CUDA_OK) return st;
+  R->plan = plan;
   BfCudaPlan *P = R->plan;
   R->device = P->device;
   const Direction &D = P->dir[0].host;
@@ -161,6 +159,24 @@ extern "C" BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, Bf
   }
   *out = R.release();
   return BF_CUDA_OK;
+}
+
+extern "C" BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, BfCudaShardRank **out) {
+  if (!rankDesc || !out) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
+  *out = nullptr;
+  BfCudaPlan *plan = nullptr;
+  BfCudaStatus st = bfCudaPlanCreate(rankDesc, &plan);
+  return st == BF_CUDA_OK ? wrapRankPlan(plan, out) : st;
+}
+
+// One rank from the file its plan was saved to (bfCudaPlanSave(bfCudaShardRankGetPlan(rank), path)): the factors
+// of a sharded operator are built once per rank and re-read afterwards.
+extern "C" BfCudaStatus bfCudaShardRankLoad(const char *path, int32_t device, BfCudaShardRank **out) {
+  if (!path || !out) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null argument");
+  *out = nullptr;
+  BfCudaPlan *plan = nullptr;
+  BfCudaStatus st = bfCudaPlanLoad(path, device, &plan);
+  return st == BF_CUDA_OK ? wrapRankPlan(plan, out) : st;
 }
 
 extern "C" BfCudaPlan *bfCudaShardRankGetPlan(BfCudaShardRank *R) { return R ? R->plan : nullptr; }

@@ -691,6 +691,7 @@ BfCudaStatus validate(const BfCudaHelm2Build *b) {
 
 extern "C" BfCudaStatus bfCudaPlanBuildHelm2(BfCudaPlan *P, const BfCudaHelm2Build *b, BfCudaHelm2Stats *stats) {
   if (!P) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "null plan");
+  if (P->loadedFromFile) return fail(BF_CUDA_ERROR_NOT_IMPLEMENTED, "a plan loaded from a file holds no per-leaf data: its values cannot be re-built");
   BfCudaStatus st = validate(b);
   if (st != BF_CUDA_OK) return st;
   if (P->dtype != BF_CUDA_COMPLEX_F64) return fail(BF_CUDA_ERROR_INVALID_ARGUMENT, "Helmholtz factors are complex");

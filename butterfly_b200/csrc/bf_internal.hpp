@@ -55,6 +55,7 @@ struct DevDirection {
   ItemDep *fItemDeps = nullptr;
   TileDep *fTileDeps = nullptr;
   uint32_t *fqItemBegin = nullptr, *fqTileBegin = nullptr;
+  size_t fNumItems = 0, fNumTiles = 0;
   uint32_t *itemPeers = nullptr; // block-row shards: per item (all stages concatenated like `items`), ranks that read its rows
   uint32_t *counters = nullptr; // [2][numCounters]
   uint32_t numCounters = 0;
@@ -75,6 +76,12 @@ struct DevDirection {
 
 constexpr size_t kStageBytes = size_t(8) << 20; // one pinned staging buffer
 constexpr uint64_t kFusedMinPoolBytes = 24ull << 30; // single-launch 1-RHS apply from this pool size on (bf_capi.cu applyImpl)
+
+namespace bfc {
+// Device tables + pool of one compiled direction (bf_capi.cu); values of leaves with host pointers are packed and
+// uploaded, the pool of a value-less direction is zeroed.
+BfCudaStatus uploadDirection(struct ::BfCudaPlan *P, DevDirection &dd);
+} // namespace bfc
 
 struct BfCudaPlan {
   int device = 0;
@@ -106,6 +113,7 @@ struct BfCudaPlan {
   size_t extWsBytes = 0;
   const bfc::ShardLaunch *shardDev = nullptr; // device copy, not owned
   uint32_t shardEpoch = 0;
+  bool loadedFromFile = false; // bfCudaPlanLoad: tables and pool only, no per-leaf host data (no value (re)build)
   int fusedMode = 2;          // bfCudaPlanSetFused / BF_CUDA_FUSED: 0 per-stage launches, 1 single launch, 2 by size
 };
 

@@ -41,6 +41,22 @@ class Plan:
         self._borrowed = True
         return self
 
+    def save(self, path):
+        """bfCudaPlanSave: tables + the device-resident factor pool, every built direction."""
+        capi.check(self.lib.bfCudaPlanSave(self.handle, str(path).encode()), "bfCudaPlanSave")
+
+    @classmethod
+    def load(cls, path, device: int = -1) -> "Plan":
+        """bfCudaPlanLoad: a plan that applies bit-identically to the saved one."""
+        lib = capi.load_library()
+        h = C.c_void_p()
+        capi.check(lib.bfCudaPlanLoad(str(path).encode(), device, C.byref(h)), "bfCudaPlanLoad")
+        i = capi.PlanInfo()
+        capi.check(lib.bfCudaPlanGetInfo(h, C.byref(i)), "bfCudaPlanGetInfo")
+        self = cls.borrow(h, i.numRows, i.numCols, i.dtype)
+        self._borrowed = False
+        return self
+
     # ------------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "handle", None):

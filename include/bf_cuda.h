@@ -254,6 +254,7 @@ typedef struct BfCudaShardHandle {
   unsigned char wsIpc[64], flagsIpc[64]; /* cudaIpcMemHandle_t */
 } BfCudaShardHandle;
 BfCudaStatus bfCudaShardRankCreate(const BfCudaPlanDesc *rankDesc, BfCudaShardRank **out);
+BfCudaStatus bfCudaShardRankLoad(const char *path, int32_t device, BfCudaShardRank **out); /* a rank plan saved with bfCudaPlanSave */
 BfCudaStatus bfCudaShardRankDestroy(BfCudaShardRank *rank);
 BfCudaPlan *bfCudaShardRankGetPlan(BfCudaShardRank *rank);
 int64_t bfCudaShardRankSentRows(const BfCudaShardRank *rank); /* workspace rows pushed to peers per apply */
@@ -386,6 +387,18 @@ BfCudaStatus bfCudaRawOpsSave(const BfCudaPlanDesc *desc, const char *path);
 /* Loads into one malloc'ed arena; free with bfCudaRawOpsFree. */
 BfCudaStatus bfCudaRawOpsLoad(const char *path, BfCudaPlanDesc **desc);
 void bfCudaRawOpsFree(BfCudaPlanDesc *desc);
+
+/* The COMPILED plan — stage tables, single-launch tables, fused permutations and the packed factor pool as it sits
+ * in HBM, every built direction — in one file.  Covers what bfCudaRawOpsSave cannot: operators whose values only
+ * ever existed on the GPU (bfCudaPlanBuildHelm2) and the per-rank plans of a block-row sharded operator
+ * (bfCudaPlanSave(bfCudaShardRankGetPlan(rank), path) / bfCudaShardRankLoad).  Reference anchors: the Dump
+ * writers that have no reader, src/mat.c:67-73, src/mat_product.c:123-140, src/mat_block_coo.c:260-289.  The pool
+ * moves through two pinned 64 MiB buffers (disk and PCIe overlap).  A loaded plan applies bit-identically to the
+ * saved one on any sm_100 device (`device` = -1: the current one); it holds no per-leaf data, so
+ * bfCudaPlanFillSynthetic / bfCudaPlanBuildHelm2 on it return NOT_IMPLEMENTED.  Truncated or corrupted files are
+ * refused (BF_CUDA_ERROR_IO): every index the kernels would follow is checked against the file's own sizes. */
+BfCudaStatus bfCudaPlanSave(BfCudaPlan *plan, const char *path);
+BfCudaStatus bfCudaPlanLoad(const char *path, int32_t device, BfCudaPlan **plan);
 
 /* ---- on-device construction of Helmholtz factor values ----------------------
  * The reference computes every leaf of a fac_helm2 operator with one of two builders:
