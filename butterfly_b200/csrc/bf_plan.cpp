@@ -26,9 +26,6 @@ static bool leafStoredTransposed(const BfCudaRawOp &o, bool cplx) {
   return (o.flags & BF_CUDA_LEAF_TRANS) != 0;
 }
 
-constexpr int64_t kFillerMaxBytes = int64_t(4) << 30;
-static bool fillerEnabled() { static const int v = std::getenv("BF_PLAN_FILLER") ? std::atoi(std::getenv("BF_PLAN_FILLER")) : 1; return v != 0; }
-
 namespace {
 struct Frag {       // one (leaf, elementary output interval) incidence
   int32_t stage;
@@ -254,66 +251,9 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     if (d.inBuf != D.inBufId && lastW[d.inBuf] < 0) {
       err = "an op reads buffer " + std::to_string(d.inBuf) + " which nothing writes"; return BF_CUDA_ERROR_INVALID_ARGUMENT;
     }
-  // ---- 2b. leaves that read the operand and write the result are FILLER -------------------------------
-  // A near-field leaf (X -> Y) depends on nothing and nothing depends on it (Y is never read), so it may run in any
-  // stage.  By the rule above they all sit in stage 0, which then holds most of the bytes (55 % at N = 16 384)
-  // while the deeper stages are so short that their launch / ramp / tail cost more than their bytes.  They are
-  // dealt out to the stages so that every stage carries about the same bytes.  Only the order in which a row of Y receives its partial sums changes
-  // (stage order; still fixed by the plan).
-  if (numStages > 1 && fillerEnabled()) {
-    const int64_t es = elemBytes(desc.dtype);
-    std::vector<int64_t> load((size_t)numStages, 0);
-    int64_t total = 0;
-    auto bytesOf = [&](const DirOp &d) { return d.remote ? int64_t(0) : (d.kind == BF_CUDA_LEAF_DENSE ? d.m * d.k * es : d.m * 8); };
-    for (const DirOp &d : D.ops) {
-      total += bytesOf(d);
-      if (!(d.inBuf == D.inBufId && d.outBuf == D.outBufId)) load[(size_t)d.stage] += bytesOf(d);
-    }
-    // (each to the stage that is the lightest at that moment: the leaves of one row block of Y end up in
-    // different stages, so no stage gets a whole row block's worth of tiles in one item.  Small operators only:
-    // a large one runs as a single launch without stage barriers, and at many RHS the extra passes over Y cost
-    // more than short stages do.)
-    if (total < kFillerMaxBytes) {
-      // every stage's deficit against the level all stages can reach; a leaf goes to the stage that still has
-      // the largest FRACTION of its deficit open, so consecutive leaves (the same rows of Y) are interleaved over
-      // the stages in proportion instead of filling the emptiest stage with one long run
-      int64_t filler = 0;
-      for (const DirOp &d : D.ops)
-        if (d.inBuf == D.inBufId && d.outBuf == D.outBufId) filler += bytesOf(d);
-      std::vector<int64_t> sorted(load);
-      std::sort(sorted.begin(), sorted.end());
-      int64_t level = 0; // water level: sum over stages of max(0, level - load) == filler
-      {
-        int64_t acc = 0;
-        for (int32_t i = 0; i < numStages; ++i) {
-          acc += sorted[(size_t)i];
-          level = (acc + filler) / (i + 1);
-          if (i + 1 == numStages || level <= sorted[(size_t)i + 1]) break;
-        }
-      }
-      std::vector<double> deficit((size_t)numStages), open((size_t)numStages);
-      for (int32_t i = 0; i < numStages; ++i) deficit[(size_t)i] = open[(size_t)i] = (double)std::max<int64_t>(level - load[(size_t)i], 0);
-      for (DirOp &d : D.ops)
-        if (d.inBuf == D.inBufId && d.outBuf == D.outBufId) {
-          int32_t st = 0;
-          double best = -1.0;
-          for (int32_t i = 0; i < numStages; ++i) {
-            const double f = deficit[(size_t)i] > 0 ? open[(size_t)i] / deficit[(size_t)i] : -1.0;
-            if (f > best) { best = f; st = i; }
-          }
-          d.stage = st;
-          open[(size_t)st] -= (double)bytesOf(d);
-          load[(size_t)st] += bytesOf(d);
-        }
-    }
-    firstW[(size_t)D.outBufId] = INT_MAX;
-    lastW[(size_t)D.outBufId] = -1;
-    for (const DirOp &d : D.ops)
-      if (d.outBuf == D.outBufId) {
-        firstW[(size_t)D.outBufId] = std::min(firstW[(size_t)D.outBufId], d.stage);
-        lastW[(size_t)D.outBufId] = std::max(lastW[(size_t)D.outBufId], d.stage);
-      }
-  }
+  // (Tried and measured slower, so NOT done: dealing the leaves that read X and write Y — which depend on nothing —
+  // out over the later stages so that every stage carries the same bytes.  N = 16 384: 0.142 -> 0.152 ms, N = 65 536:
+  // 0.578 -> 0.616 ms; the extra, smaller items on Y cost more than the short stages do.  profiles/r2i_plan_knobs.txt)
   D.stages.assign((size_t)numStages, Stage());
 
   // ---- 3. workspace: ping-pong arenas keyed by the parity of the stage that READS a buffer ----
