@@ -50,6 +50,7 @@ def parse():
                          "(0 = the reference's rule; 4 gives a far more accurate operator, DESIGN.md 8c)")
     ap.add_argument("--no-extra", action="store_true", help="skip the 256-RHS side measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-1m", action="store_true", help="multi-GPU runs (>= 4 GPUs): skip the 2^20-point block-row sharded side block")
     return ap.parse_args()
 
 
@@ -682,7 +683,7 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:
             gpu_build = {"error": str(e)[:200]}
 
-    rows_extra = None
+    rows_extra = rows_1m = None
     if not args.no_extra and nrhs == 1 and world > 1:
         # side measurement, configs[4]: the SAME operator block-row sharded over the ranks (strong scaling)
         plan.close()
@@ -695,6 +696,14 @@ def run_ours(args, rank, local_rank, world):
                                   solve=args.solve or 10)
         except Exception as e:
             rows_extra = {"error": str(e)[:300]}
+        # configs[1] / configs[4] at their own size: 2^20 points, 186 GB of factors — more than one B200 holds, so it
+        # only exists block-row sharded (>= 4 GPUs: 46 GB per rank).  Real values, built per rank on the GPU; checked
+        # against dense kernel rows (no unsharded plan to compare with: it does not fit).
+        if world >= 4 and not args.no_1m:
+            try:
+                rows_1m = run_rows(args, rank, local_rank, world, n=1 << 20, steps=10, warmup=2, verify=False, solve=0)
+            except Exception as e:
+                rows_1m = {"error": str(e)[:300]}
 
     cpu = configs0 = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -730,6 +739,7 @@ def run_ours(args, rank, local_rank, world):
             "lbo_real": lbo,
             "helm2_gpu_build": gpu_build,
             "row_shard": rows_extra,
+            "row_shard_1M": rows_1m,
         }
         print(json.dumps(line), flush=True)
     plan.close()  # idempotent
