@@ -8,6 +8,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "bf_internal.hpp"
@@ -52,22 +53,59 @@ BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
   }
   const size_t poolBytes = (size_t)D.pool16 * 16 + 256; // slack: nothing reads it, keeps zero-size plans valid
   BF_CUDA_TRY(cudaMalloc(&dd.pool, poolBytes));
+  BF_CUDA_TRY(cudaMemsetAsync(dd.pool, 0, poolBytes, P->stream)); // (ops without host values stay zero)
   bool anyVal = false;
   for (const DirOp &d : D.ops) if (d.val) { anyVal = true; break; }
   if (anyVal) {
-    // pack stage by stage through a bounded host buffer
-    size_t maxStage = 0;
-    for (const Stage &S : D.stages) maxStage = std::max(maxStage, (size_t)(S.poolEnd16 - S.poolBegin16) * 16);
-    std::unique_ptr<unsigned char[]> hostBuf(new (std::nothrow) unsigned char[std::max<size_t>(maxStage, 16)]);
-    if (!hostBuf) return fail(BF_CUDA_ERROR_OUT_OF_MEMORY, "host staging buffer for the value pool");
-    for (size_t s = 0; s < nS; ++s) {
+    // Pack chunk by chunk (whole tiles, <= kPackChunk bytes) into two pinned buffers: the host threads pack chunk
+    // c + 1 while the DMA engine moves chunk c.  (A single thread through an unpinned buffer with blocking copies
+    // moved 2 GB/s: 1.65 s to attach the 3.3 GB operator of N = 65 536.)
+    constexpr size_t kPackChunk = size_t(32) << 20;
+    unsigned char *pin[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    cudaStream_t up = P->stream;
+    auto cleanup = [&]() { for (int i = 0; i < 2; ++i) { if (pin[i]) cudaFreeHost(pin[i]); if (ev[i]) cudaEventDestroy(ev[i]); } };
+    for (int i = 0; i < 2; ++i)
+      if (cudaHostAlloc(&pin[i], kPackChunk + kTileBytes, cudaHostAllocDefault) != cudaSuccess || cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess) {
+        cleanup();
+        return fail(BF_CUDA_ERROR_OUT_OF_MEMORY, "pinned staging buffers for the value pool");
+      }
+    const unsigned nThreads = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    size_t chunkNo = 0;
+    cudaError_t ce = cudaSuccess;
+    for (size_t s = 0; s < nS && ce == cudaSuccess; ++s) {
       const Stage &S = D.stages[s];
-      const size_t bytes = (size_t)(S.poolEnd16 - S.poolBegin16) * 16;
-      if (!bytes) continue;
-      std::memset(hostBuf.get(), 0, bytes);
-      packPool(D, s, s + 1, hostBuf.get());
-      BF_CUDA_TRY(cudaMemcpy(dd.pool + S.poolBegin16 * 16, hostBuf.get(), bytes, cudaMemcpyHostToDevice));
+      const size_t nT = S.tiles.size();
+      for (size_t t0 = 0; t0 < nT && ce == cudaSuccess;) {
+        const uint64_t base16 = S.tilePool16[t0];
+        size_t t1 = t0;
+        uint64_t end16 = base16;
+        while (t1 < nT) { // whole tiles up to the chunk size
+          const uint64_t e = S.tilePool16[t1] + tileBytes16(D.dtype, S.tiles[t1].rows, S.tiles[t1].kc);
+          if ((e - base16) * 16 > kPackChunk && t1 > t0) break;
+          end16 = e;
+          ++t1;
+        }
+        const size_t bytes = (size_t)(end16 - base16) * 16;
+        if (bytes) {
+          const int b = (int)(chunkNo & 1);
+          if (chunkNo >= 2) ce = cudaEventSynchronize(ev[b]); // the copy out of this buffer has finished
+          std::memset(pin[b], 0, bytes);
+          std::vector<std::thread> th;
+          const size_t per = (t1 - t0 + nThreads - 1) / nThreads;
+          for (unsigned k = 0; k < nThreads && t0 + k * per < t1; ++k)
+            th.emplace_back([&, k]() { packTileRange(D, s, t0 + k * per, std::min(t1, t0 + (k + 1) * per), base16, pin[b]); });
+          for (std::thread &x : th) x.join();
+          if (ce == cudaSuccess) ce = cudaMemcpyAsync(dd.pool + base16 * 16, pin[b], bytes, cudaMemcpyHostToDevice, up);
+          if (ce == cudaSuccess) ce = cudaEventRecord(ev[b], up);
+          ++chunkNo;
+        }
+        t0 = t1;
+      }
     }
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(up);
+    cleanup();
+    if (ce != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("value pool upload: ") + cudaGetErrorString(ce));
   } else {
     BF_CUDA_TRY(cudaMemset(dd.pool, 0, poolBytes));
   }

@@ -591,16 +591,16 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
 template <typename T> static inline T conjIf(T v, bool) { return v; }
 template <> inline std::complex<double> conjIf(std::complex<double> v, bool c) { return c ? std::conj(v) : v; }
 
+// tiles [t0, t1) of stage S; base[0] corresponds to pool offset base16
 template <typename T>
-static void packStage(const Direction &dir, const Stage &S, T *base /* pool offset poolBegin16 */) {
-  const size_t nT = S.tiles.size();
-  for (size_t t = 0; t < nT; ++t) {
+static void packStage(const Direction &dir, const Stage &S, T *base, size_t t0, size_t t1, uint64_t base16) {
+  for (size_t t = t0; t < t1; ++t) {
     const DevTile &tl = S.tiles[t];
     if (tl.kc == kKcIdentity) continue;
     const PieceRef &pr = S.pieces[t];
     const DirOp &d = dir.ops[(size_t)pr.op];
     if (!d.val) continue;
-    char *dstBytes = reinterpret_cast<char *>(base) + 16 * (S.tilePool16[t] - S.poolBegin16);
+    char *dstBytes = reinterpret_cast<char *>(base) + 16 * (S.tilePool16[t] - base16);
     if (tl.kc == kKcDiag) { // real diagonal values, also on a complex operator (src/mat_diag_real.c:168)
       double *dst = reinterpret_cast<double *>(dstBytes);
       const double *src = static_cast<const double *>(d.val);
@@ -623,9 +623,15 @@ void packPool(const Direction &dir, size_t s0, size_t s1, void *dst) {
   for (size_t s = s0; s < s1; ++s) {
     const Stage &S = dir.stages[s];
     char *base = static_cast<char *>(dst) + 16 * (S.poolBegin16 - dir.stages[s0].poolBegin16);
-    if (dir.dtype == BF_CUDA_COMPLEX_F64) packStage(dir, S, reinterpret_cast<std::complex<double> *>(base));
-    else packStage(dir, S, reinterpret_cast<double *>(base));
+    if (dir.dtype == BF_CUDA_COMPLEX_F64) packStage(dir, S, reinterpret_cast<std::complex<double> *>(base), 0, S.tiles.size(), S.poolBegin16);
+    else packStage(dir, S, reinterpret_cast<double *>(base), 0, S.tiles.size(), S.poolBegin16);
   }
+}
+
+void packTileRange(const Direction &dir, size_t stage, size_t t0, size_t t1, uint64_t base16, void *dst) {
+  const Stage &S = dir.stages[stage];
+  if (dir.dtype == BF_CUDA_COMPLEX_F64) packStage(dir, S, reinterpret_cast<std::complex<double> *>(dst), t0, t1, base16);
+  else packStage(dir, S, reinterpret_cast<double *>(dst), t0, t1, base16);
 }
 
 } // namespace bfc

@@ -171,6 +171,9 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
 // Pack the values of stages [s0, s1) into dst (dst[0] corresponds to pool offset
 // stages[s0].poolBegin16).  Ops with val == NULL are left zero.
 void packPool(const Direction &dir, size_t s0, size_t s1, void *dst);
+// The same for tiles [t0, t1) of one stage; dst[0] corresponds to pool offset base16 (<= tilePool16[t0]).  Ranges of
+// different tiles write disjoint bytes, so several threads may pack one buffer.
+void packTileRange(const Direction &dir, size_t stage, size_t t0, size_t t1, uint64_t base16, void *dst);
 
 // Deterministic synthetic value of stored element `linear` (= storedRow * storedCols + storedCol)
 // of raw op `rawIndex`; part 0 = real, 1 = imaginary; uniform in [-scale, scale).  Integer hash +
