@@ -659,6 +659,32 @@ def run_ours(args, rank, local_rank, world):
                 lbo[name] = {"ms_per_apply": ms, "gflops": 2.0 * EL / (ms * 1e-3) / 1e9, "matvecs_per_s": 1e3 / ms,
                              "gbs": byts / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": byts / (ms * 1e-3) / 1e9 / peaks()[0],
                              "launches": int(planL.last_launch_count)}
+            # the real many-RHS kernel (bfWideStage<real>: register-blocked DFMA; the reference has no real block apply at
+            # all): 64 columns, against the DFMA ceiling measured on this device
+            try:
+                import ctypes as C
+
+                dfma, dmma = C.c_double(), C.c_double()
+                capi.check(capi.load_library().bfCudaMeasureFp64Peak(local_rank, C.byref(dfma), C.byref(dmma)), "bfCudaMeasureFp64Peak")
+                nr = 64
+                Xw = torch.randn(rawL.num_cols, nr, dtype=torch.float64, device="cuda")
+                Yw = torch.empty(rawL.num_rows, nr, dtype=torch.float64, device="cuda")
+                for _ in range(2):
+                    planL.apply_device(Xw, Yw, stream=stream)
+                torch.cuda.synchronize()
+                b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                b0.record()
+                for _ in range(5):
+                    planL.apply_device(Xw, Yw, stream=stream)
+                b1.record()
+                torch.cuda.synchronize()
+                ms = b0.elapsed_time(b1) / 5
+                tf = 2.0 * EL * nr / (ms * 1e-3) / 1e12
+                lbo["forward_64rhs"] = {"ms_per_apply": ms, "tflops": tf, "kernel": "bfWideStage<real> (DFMA)", "dfma_peak_tflops": dfma.value,
+                                        "frac_of_dfma_peak": tf / dfma.value if dfma.value else None, "matvecs_per_s": nr / (ms * 1e-3)}
+                del Xw, Yw
+            except Exception as e:
+                lbo["forward_64rhs"] = {"error": str(e)[:200]}
             planL.close()
         except Exception as e:
             lbo = {"error": str(e)[:200]}
