@@ -106,9 +106,10 @@ BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(up);
     cleanup();
     if (ce != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("value pool upload: ") + cudaGetErrorString(ce));
-  } else {
-    BF_CUDA_TRY(cudaMemset(dd.pool, 0, poolBytes));
   }
+  // (a value-less plan keeps the zeros of the memset above: it is ordered on P->stream, like the synthetic fill that
+  // follows.  A second cudaMemset here ran on the LEGACY stream, which a non-blocking stream does not wait for, and
+  // could zero tiles the fill had already written.)
   if (D.shardWorld > 1) { // block-row shard: which ranks read which item's rows
     std::vector<uint32_t> peers;
     peers.reserve(nI);
@@ -133,14 +134,18 @@ BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
     BF_CUDA_TRY(up(&dd.fqTileBegin, F.qTileBegin));
     dd.numCounters = F.numCounters;
     BF_CUDA_TRY(cudaMalloc(&dd.counters, std::max<size_t>(2 * (size_t)F.numCounters, 1) * sizeof(uint32_t)));
-    BF_CUDA_TRY(cudaMemset(dd.counters, 0, std::max<size_t>(2 * (size_t)F.numCounters, 1) * sizeof(uint32_t)));
+    BF_CUDA_TRY(cudaMemsetAsync(dd.counters, 0, std::max<size_t>(2 * (size_t)F.numCounters, 1) * sizeof(uint32_t), P->stream));
     dd.fusedWsRows = F.wsRows;
     dd.tableBytes += (int64_t)(F.items.size() * 24 + F.tiles.size() * 16 + 2 * (Q + 1) * 4 + 2 * (size_t)F.numCounters * 4);
     dd.fusedReady = true;
     dd.fNumItems = F.items.size(); dd.fNumTiles = F.tiles.size();
     F.items = {}; F.itemDeps = {}; F.tiles = {}; F.tileDeps = {}; // device-resident now
   }
-  (void)P;
+  // The tables went up with cudaMemcpy from pageable memory: it returns once the data is STAGED, the DMA itself runs
+  // on the legacy stream, which the plan's non-blocking stream (and the caller's) does not wait for.  Land everything
+  // before the first apply can be enqueued.
+  BF_CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy));
+  BF_CUDA_TRY(cudaStreamSynchronize(P->stream));
   dd.built = true;
   return BF_CUDA_OK;
 }
@@ -262,6 +267,7 @@ static BfCudaStatus uploadPerm(const int64_t *perm, int64_t n, int32_t **dFwd, i
   BF_CUDA_TRY(cudaMalloc(dInv, std::max<size_t>((size_t)n, 1) * 4));
   BF_CUDA_TRY(cudaMemcpy(*dFwd, f.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
   BF_CUDA_TRY(cudaMemcpy(*dInv, inv.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+  BF_CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy)); // pageable copies: landed before an apply on another stream reads them
   return BF_CUDA_OK;
 }
 
@@ -639,7 +645,9 @@ BfCudaStatus bfCudaPlanFillSynthetic(BfCudaPlan *P, uint64_t seed) {
       }
       FillPiece *dp = nullptr;
       BF_CUDA_TRY(cudaMalloc(&dp, nT * sizeof(FillPiece)));
-      cudaError_t e = cudaMemcpy(dp, fp.data(), nT * sizeof(FillPiece), cudaMemcpyHostToDevice);
+      // (stream-ordered with the fill kernel; a plain cudaMemcpy from pageable memory returns before its DMA has
+      // landed and the plan's stream is non-blocking)
+      cudaError_t e = cudaMemcpyAsync(dp, fp.data(), nT * sizeof(FillPiece), cudaMemcpyHostToDevice, P->stream);
       if (e == cudaSuccess) e = launchFillSynthetic(P->dtype, dd.pool, dp, (long long)nT, seed, P->stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(P->stream);
       cudaFree(dp);

@@ -148,6 +148,8 @@ static BfCudaStatus wrapRankPlan(BfCudaPlan *plan, BfCudaShardRank **out) {
   if ((e = cudaMalloc(&R->done, (size_t)R->numStages * 4)) != cudaSuccess) return bail(e, "done counters");
   if ((e = cudaMemset(R->done, 0, (size_t)R->numStages * 4)) != cudaSuccess) return bail(e, "done counters");
   if ((e = cudaMalloc(&R->dev, sizeof(ShardLaunch))) != cudaSuccess) return bail(e, "launch context");
+  // the memsets above run on the legacy stream; the stage kernels (and peers) use non-blocking streams
+  if ((e = cudaStreamSynchronize(cudaStreamLegacy)) != cudaSuccess) return bail(e, "workspace clear");
   ShardLaunch &h = R->host;
   h.world = R->world; h.rank = R->rank; h.numStages = R->numStages;
   h.done = R->done;
@@ -241,6 +243,7 @@ extern "C" BfCudaStatus bfCudaShardRankConnect(BfCudaShardRank *R, const BfCudaS
     }
   }
   BF_CUDA_TRY(cudaMemcpy(R->dev, &R->host, sizeof(ShardLaunch), cudaMemcpyHostToDevice));
+  BF_CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy)); // landed before a stage kernel on a non-blocking stream reads it
   R->plan->extWs = R->ws;
   R->plan->extWsBytes = R->wsBytes;
   R->plan->shardDev = R->dev;

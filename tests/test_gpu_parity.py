@@ -181,3 +181,38 @@ def test_single_launch_apply_is_bit_identical_to_per_stage_launches(case, op):
             assert np.array_equal(y, y_staged), "fused and per-stage results differ"
     assert stages >= plan.last_launch_count
     assert _relerr(y_staged, portlib.apply(raw, x, op)) <= TOL
+
+
+def test_synthetic_fill_right_after_create_with_several_live_plans():
+    """Regression: the plan's stream is non-blocking, so nothing of plan creation or of the synthetic fill may be
+    left on the legacy stream (a cudaMemset of the pool, pageable cudaMemcpy of the tables) when the fill kernel
+    or the first apply starts.  Six plans created and filled back to back once left one of them with a partly
+    zeroed pool.  Every plan must agree with the first one, and a re-fill must change nothing."""
+    import torch
+
+    raw = synth.random_hodbf(n=24000, dtype=capi.COMPLEX_F64, seed=19, leaf=64, rank_lo=16, rank_hi=40, with_values=False, exotic=False)
+    x = torch.from_numpy(_x(np.random.default_rng(4), raw.num_cols, 1, True)).cuda()
+    stream = torch.cuda.current_stream().cuda_stream
+    plans = []
+    try:
+        for _ in range(5):
+            p = Plan(raw)
+            p.fill_synthetic(11)
+            plans.append(p)
+        ys = []
+        for p in plans:
+            y = torch.empty_like(x)
+            for _ in range(3):
+                p.apply_device(x, y, stream=stream)
+            torch.cuda.synchronize()
+            ys.append(y)
+        for y in ys[1:]:
+            assert torch.equal(y, ys[0])
+        plans[0].fill_synthetic(11)
+        y = torch.empty_like(x)
+        plans[0].apply_device(x, y, stream=stream)
+        torch.cuda.synchronize()
+        assert torch.equal(y, ys[0])
+    finally:
+        for p in plans:
+            p.close()
