@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <map>
 #include <queue>
 
 namespace bfc {
@@ -29,9 +30,22 @@ static bool leafStoredTransposed(const BfCudaRawOp &o, bool cplx) {
 
 static bool sortItemsEnabled() { static const int v = std::getenv("BF_PLAN_SORT") ? std::atoi(std::getenv("BF_PLAN_SORT")) : 1; return v != 0; }
 
-static uint64_t itemCost(int dtype, const Stage &S, const DevItem &it) {
-  uint64_t c = 256 + 32ull * it.rows;
-  for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) c += 16 * tileBytes16(dtype, S.tiles[t].rows, S.tiles[t].kc) + 384;
+static bool deferHeavyEnabled() { const char *e = std::getenv("BF_PLAN_DEFER"); return !e || std::atoi(e) != 0; } // read per compile (A/B in one process)
+
+// Cost model of the queue assignment, in byte equivalents: what a warp spends on a tile besides streaming its bytes.
+// A tile is a serial chain for its warp (descriptor shuffles, mbarrier wait, shared-memory loads, a dependent FMA
+// chain, the refill's bulk-copy issue): about as long as streaming 12 KiB once the stage is short enough that warps
+// run alone at its end.  Measured (tools/plan_knob_ab.py, profiles/r2z_plan_tile_cost.txt): with 384 the queues of
+// stage 0 at N = 16 384 carried 24 .. 92 tiles for near-equal bytes and the apply took 0.131 ms; with 12 288 they
+// carry 38 .. 51 and it takes 0.107 ms (N = 65 536: 0.546 -> 0.527 ms; N = 524 288, HBM-bound: unchanged).
+// Development knobs, read per compile: BF_PLAN_TILE_COST, BF_PLAN_ITEM_COST.
+static uint64_t tileFixedCost() { const char *e = std::getenv("BF_PLAN_TILE_COST"); return e ? (uint64_t)std::atoll(e) : 12288ull; }
+
+static uint64_t itemFixedCost() { const char *e = std::getenv("BF_PLAN_ITEM_COST"); return e ? (uint64_t)std::atoll(e) : 256ull; }
+
+static uint64_t itemCost(int dtype, const Stage &S, const DevItem &it, uint64_t tileCost, uint64_t itemFixed) {
+  uint64_t c = itemFixed + 32ull * it.rows;
+  for (uint32_t t = it.tileBegin; t < it.tileBegin + it.numTiles; ++t) c += 16 * tileBytes16(dtype, S.tiles[t].rows, S.tiles[t].kc) + tileCost;
   return c;
 }
 
@@ -46,7 +60,9 @@ static std::vector<uint32_t> assignItemsLpt(int dtype, Stage &S, int numQueues) 
   std::vector<uint32_t> qEnd((size_t)numQueues, (uint32_t)nI);
   if (nI == 0) return qEnd;
   std::vector<uint64_t> cost(nI);
-  for (size_t i = 0; i < nI; ++i) cost[i] = itemCost(dtype, S, S.items[i]);
+  const uint64_t tileCost = tileFixedCost();
+  const uint64_t itemFixed = itemFixedCost();
+  for (size_t i = 0; i < nI; ++i) cost[i] = itemCost(dtype, S, S.items[i], tileCost, itemFixed);
   std::vector<uint32_t> order(nI);
   std::iota(order.begin(), order.end(), 0u);
   std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
@@ -445,6 +461,68 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
     if (a.elem != b.elem) return a.elem < b.elem;
     return a.seq < b.seq;
   });
+
+  // ---- 4b. result rows too long for one queue ------------------------------------------------------
+  // An item is at least 8 rows of an elementary interval with ALL the leaves that write those rows at that stage,
+  // and it is read by one warp.  On a small operator the near-field leaves of one block row (X -> Y, stage 0) can
+  // exceed a queue's share of the stage even at 8 rows (N = 16 384: 283 KB against 174 KB, 48 such items): every
+  // other queue then waits for them (SM sub-partitions active 63 % of stage 0, ncu r2y).  Leaves that read the
+  // operand and write the result depend on nothing and may run at ANY stage (later stages accumulate), so the
+  // excess is handed, leaf by leaf, to the later stage where the same rows are lightest relative to that stage's
+  // share.  (Dealing ALL such leaves out evenly was measured slower — see step 2; this moves a few percent of
+  // stage 0.)  Only the frag moves: the summation order of those rows changes, nothing else.
+  if (!sharded && numStages > 1 && deferHeavyEnabled()) {
+    const int64_t es = desc.dtype == BF_CUDA_COMPLEX_F64 ? 16 : 8;
+    std::vector<int64_t> sBytes((size_t)numStages, 0);
+    std::map<std::pair<int32_t, int64_t>, int64_t> rowBytesOf; // (stage, elem) -> bytes per row
+    for (const Frag &fr : frags)
+      if (fr.seq >= 0 && D.ops[(size_t)fr.seq].kind == BF_CUDA_LEAF_DENSE) {
+        sBytes[(size_t)fr.stage] += elems[(size_t)fr.elem].len * D.ops[(size_t)fr.seq].k * es;
+        rowBytesOf[{fr.stage, fr.elem}] += D.ops[(size_t)fr.seq].k * es;
+      }
+    std::vector<double> share((size_t)numStages);
+    for (int32_t t = 0; t < numStages; ++t) share[(size_t)t] = std::max<double>(1.0, (double)sBytes[(size_t)t] / std::max(numQueues, 1));
+    bool moved = false;
+    for (size_t f = 0; f < frags.size();) {
+      size_t f1 = f;
+      while (f1 < frags.size() && frags[f1].stage == frags[f].stage && frags[f1].elem == frags[f].elem) ++f1;
+      const Elem &el = elems[(size_t)frags[f].elem];
+      const int32_t s = frags[f].stage;
+      const size_t g0 = f, g1 = f1;
+      f = f1;
+      if (el.buf != D.outBufId || frags[g0].seq < 0 || s + 1 >= numStages) continue;
+      const double rowsMin = (double)std::min<int64_t>(el.len, 8);
+      int64_t kept = rowBytesOf[{s, frags[g0].elem}];
+      if (rowsMin * (double)kept <= 1.1 * share[(size_t)s]) continue;
+      size_t left = g1 - g0;
+      for (size_t q = g1; q-- > g0 && left > 1;) {
+        const DirOp &d = D.ops[(size_t)frags[q].seq];
+        if (d.kind != BF_CUDA_LEAF_DENSE || d.inBuf != D.inBufId) continue;
+        if (rowsMin * (double)kept <= share[(size_t)s]) break;
+        const int64_t rb = d.k * es;
+        int32_t best = -1;
+        double bestRatio = rowsMin * (double)kept / share[(size_t)s]; // moving must leave the rows lighter there than here
+        for (int32_t t = s + 1; t < numStages; ++t) {
+          auto itT = rowBytesOf.find({t, frags[q].elem});
+          const double have = itT == rowBytesOf.end() ? 0.0 : (double)itT->second;
+          const double ratio = rowsMin * (have + (double)rb) / share[(size_t)t];
+          if (ratio < bestRatio) { bestRatio = ratio; best = t; }
+        }
+        if (best < 0) continue;
+        rowBytesOf[{best, frags[q].elem}] += rb;
+        kept -= rb;
+        frags[q].stage = best;
+        --left;
+        moved = true;
+      }
+    }
+    if (moved)
+      std::sort(frags.begin(), frags.end(), [](const Frag &a, const Frag &b) {
+        if (a.stage != b.stage) return a.stage < b.stage;
+        if (a.elem != b.elem) return a.elem < b.elem;
+        return a.seq < b.seq;
+      });
+  }
 
   // ---- 5. items and tiles per stage -------------------------------------------------------------
   // An item is read by ONE warp (1-RHS kernel), so an item much longer than a queue's share of its

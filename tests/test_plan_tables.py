@@ -93,3 +93,56 @@ def test_oracle_transpose_is_adjoint():
     lhs = np.vdot(y, portlib.apply(raw, x, capi.OP_N))
     rhs = np.vdot(portlib.apply(raw, y, capi.OP_H), x)
     assert abs(lhs - rhs) / abs(lhs) < 1e-12
+
+
+def _heavy_row_operator(seed=31):
+    """A HODLR-of-butterflies operator plus one block row whose near-field leaves (X -> Y) are far longer than a
+    queue's share of stage 0: the shape that left one warp working alone at N = 16 384 (bf_plan.cpp, step 4b)."""
+    from butterfly_b200.synth import _Builder, _hodlr
+
+    n = 1536
+    rng = np.random.default_rng(seed)
+    b = _Builder(capi.COMPLEX_F64, True, rng)
+    _hodlr(b, 0, n, 48, 9, 23, False)
+    for j in range(12):  # rows 200..239 get 12 x 120 more columns
+        b.dense(0, 40 + 120 * j, 1, 200, 40, 120, trans=(j % 3 == 1))
+    return b.finish(n, n)
+
+
+def _stage_entries(t):
+    """matrix entries streamed per stage (dense tiles only)"""
+    out = []
+    for s in range(t.num_stages):
+        tl = t.tiles[t.stage_tile[s]:t.stage_tile[s + 1]]
+        kc, rows = tl["kc"].astype(np.int64), tl["rows"].astype(np.int64)
+        out.append(int((rows * kc)[kc < 0xFFFD].sum()))
+    return out
+
+
+@pytest.mark.parametrize("op", [capi.OP_N, capi.OP_T])
+def test_long_result_rows_are_spread_over_later_stages(op, monkeypatch):
+    raw = _heavy_row_operator()
+    x = _x(np.random.default_rng(5), raw.num_cols if op == capi.OP_N else raw.num_rows, 2, True)
+    y_ref = portlib.apply(raw, x, op)
+    monkeypatch.setenv("BF_PLAN_DEFER", "0")
+    t0 = Tables(raw, op, num_queues=96)
+    monkeypatch.setenv("BF_PLAN_DEFER", "1")
+    t1 = Tables(raw, op, num_queues=96)
+    try:
+        for t in (t0, t1):
+            t.check_queues()
+            y = t.apply(x)
+            assert not np.isnan(y).any()
+            assert np.linalg.norm(y - y_ref) <= 1e-13 * np.linalg.norm(y_ref)
+        c0, c1 = _stage_entries(t0), _stage_entries(t1)
+        assert sum(c0) == sum(c1), "deferral moves leaves between stages, it does not add or drop entries"
+        if op == capi.OP_N:  # (transposed, the long rows become long columns: many short items, nothing to move)
+            assert c1[0] < c0[0], "nothing was moved out of stage 0"
+        assert t1.fused
+        y1 = t1.apply(x)
+        for order, seed in (("reverse", 0), ("random", 3)):
+            yf, _ = t1.apply_fused(x, order, seed)
+            assert np.array_equal(yf, y1), order
+    finally:
+        t0.close()
+        t1.close()
