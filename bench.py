@@ -688,6 +688,60 @@ def run_ours(args, rank, local_rank, world):
             planL.close()
         except Exception as e:
             lbo = {"error": str(e)[:200]}
+        # the same path on a REFERENCE-structured real operator: bfFacStreamer (src/fac_streamer.c:386-518) run offline
+        # by tools/make_lbo_fixture.py on sphere points x real spherical harmonics; the fixture carries the flattened
+        # operator, seeded operands and the reference's own bfMatMulVec / bfMatRmulVec results and CPU times
+        fx = ROOT / "fixtures" / "lbo_sphere"
+        if lbo is not None and Path(str(fx) + ".raw.npz").exists() and Path(str(fx) + ".ref.npz").exists():
+            try:
+                from butterfly_b200.rawops import RawOps
+
+                rawF = RawOps.load(str(fx) + ".raw.npz")
+                ref = np.load(str(fx) + ".ref.npz")
+                planF = Plan(rawF, device=local_rank, build_transpose=1)
+                EF = planF.info["numEntries"]
+                blk = {"workload": f"sphere n={int(ref['n'])} x real spherical harmonics l<={int(ref['lmax'])} ({rawF.num_rows} x {rawF.num_cols}), "
+                                   f"streamed by the unmodified reference (tol {float(ref['tol']):g})",
+                       "structure": "reference bfFacStreamer (fixture built offline by tools/make_lbo_fixture.py)", "E": int(EF), "dtype": "f64",
+                       "entries_over_dense": EF / (rawF.num_rows * rawF.num_cols), "reference_build_s": float(ref["reference_build_s"]),
+                       "butterfly_vs_dense_rel_l2": float(ref["butterfly_vs_dense_rel_l2"]), "tolerance": 1e-12}
+                for name, op, xk, yk, ck in (("forward", capi.OP_N, "X", "Y", "cpu_forward_ms"), ("transpose", capi.OP_T, "XT", "YT", "cpu_transpose_ms")):
+                    Xh, Yref = ref[xk], ref[yk]
+                    worst = 0.0
+                    for j in range(Xh.shape[1]):
+                        yj = planF.apply_host(np.ascontiguousarray(Xh[:, j:j + 1]), op)
+                        worst = max(worst, float(np.linalg.norm(yj[:, 0] - Yref[:, j]) / np.linalg.norm(Yref[:, j])))
+                    Yb = planF.apply_host(np.ascontiguousarray(Xh), op)  # all stored columns as one block (the wide kernel)
+                    blockerr = float(np.linalg.norm(Yb - Yref) / np.linalg.norm(Yref))
+                    xv = torch.from_numpy(np.ascontiguousarray(Xh[:, :1])).cuda()
+                    yv = torch.empty(Yref.shape[0], 1, dtype=torch.float64, device="cuda")
+                    for _ in range(5):
+                        planF.apply_device(xv, yv, op=op, stream=stream)
+                    torch.cuda.synchronize()
+                    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    reps = 200
+                    b0.record()
+                    for _ in range(reps):
+                        planF.apply_device(xv, yv, op=op, stream=stream)
+                    b1.record()
+                    torch.cuda.synchronize()
+                    ms = b0.elapsed_time(b1) / reps
+                    byts = 8.0 * EF + 8.0 * (Xh.shape[0] + Yref.shape[0])
+                    t0 = time.perf_counter()
+                    for _ in range(20):
+                        planF.apply_host(np.ascontiguousarray(Xh[:, :1]), op)
+                    host_ms = (time.perf_counter() - t0) / 20 * 1e3
+                    blk[name] = {"rel_l2_vs_reference_1rhs_max": worst, "rel_l2_vs_reference_block": blockerr, "vectors": int(Xh.shape[1]),
+                                 "device_ms_per_apply": ms, "gbs": byts / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": byts / (ms * 1e-3) / 1e9 / peaks()[0],
+                                 "l2_note": "operator smaller than L2: the pool stays L2-resident between applies, the HBM fraction is not a roofline here" if 8.0 * EF < 100e6 else "operator larger than L2",
+                                 "host_buffers_ms_per_apply": host_ms, "reference_cpu_ms_per_apply": float(ref[ck]), "cpu_cores": 1,
+                                 "speedup_host_buffers_vs_reference": float(ref[ck]) / host_ms, "launches": int(planF.last_launch_count)}
+                planF.close()
+                lbo["reference_structure"] = blk
+            except Exception as e:
+                lbo["reference_structure"] = {"error": str(e)[:300]}
+        elif lbo is not None:
+            lbo["reference_structure"] = {"unavailable": "fixtures/lbo_sphere.{raw,ref}.npz not present (python tools/make_lbo_fixture.py builds them: minutes of the reference's streamer)"}
 
     gpu_build = None
     if not args.no_extra and nrhs == 1 and world == 1:

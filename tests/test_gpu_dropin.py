@@ -187,3 +187,26 @@ def test_mulvec_rmulvec_through_swapped_vtable():
     assert np.linalg.norm(y_gpu - y_cpu) / np.linalg.norm(y_cpu) <= TOL
     assert np.linalg.norm(z_gpu - z_cpu) / np.linalg.norm(z_cpu) <= TOL
     assert np.array_equal(y_back, y_cpu)
+
+
+def test_reference_streamed_fixture_parity():
+    """configs[3] above toy size: the operator tools/make_lbo_fixture.py had the unmodified reference stream
+    (bfFacStreamer on sphere points x real spherical harmonics), applied on the GPU, against the reference's own
+    bfMatMulVec / bfMatRmulVec results stored with it.  The fixture is built offline (minutes) and is not in git."""
+    from pathlib import Path
+
+    from butterfly_b200.rawops import RawOps
+
+    fx = Path(__file__).resolve().parent.parent / "fixtures" / "lbo_sphere"
+    if not (Path(str(fx) + ".raw.npz").exists() and Path(str(fx) + ".ref.npz").exists()):
+        pytest.skip("fixtures/lbo_sphere.* not built (python tools/make_lbo_fixture.py)")
+    raw = RawOps.load(str(fx) + ".raw.npz")
+    ref = np.load(str(fx) + ".ref.npz")
+    with Plan(raw, build_transpose=1) as plan:
+        for op, xk, yk in ((capi.OP_N, "X", "Y"), (capi.OP_T, "XT", "YT")):
+            X, Yref = ref[xk], ref[yk]
+            for j in range(X.shape[1]):
+                y = plan.apply_host(np.ascontiguousarray(X[:, j:j + 1]), op)[:, 0]
+                assert np.linalg.norm(y - Yref[:, j]) / np.linalg.norm(Yref[:, j]) <= TOL
+            Y = plan.apply_host(np.ascontiguousarray(X), op)  # the same columns as one block
+            assert np.linalg.norm(Y - Yref) / np.linalg.norm(Yref) <= TOL

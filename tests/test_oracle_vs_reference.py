@@ -168,3 +168,26 @@ def test_sphere_fixture_golden_is_reproducible():
     y, _ = s.mulvec(io["x"])
     assert np.linalg.norm(y - io["y"]) / np.linalg.norm(io["y"]) < 1e-14
     assert np.array_equal(s.row_perm(), io["row_perm"])
+
+
+def test_lbo_fixture_generator_round_trip(tmp_path):
+    """tools/make_lbo_fixture.py (the offline producer of the bench's reference-structured real operator): the raw
+    ops it writes reproduce, through the port oracle, the reference results it stores beside them."""
+    import subprocess
+    import sys
+
+    from butterfly_b200.rawops import RawOps
+
+    root = Path(__file__).resolve().parent.parent
+    out = tmp_path / "lbo_tiny"
+    r = subprocess.run([sys.executable, str(root / "tools" / "make_lbo_fixture.py"), "--n", "600", "--lmax", "11", "--vectors", "2", "--out", str(out)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    raw = RawOps.load(str(out) + ".raw.npz")
+    ref = np.load(str(out) + ".ref.npz")
+    assert raw.dtype == capi.REAL_F64 and raw.num_rows == 600 and raw.num_cols == 144
+    assert float(ref["butterfly_vs_dense_rel_l2"]) < 5e-3  # the streamer's own tolerance (1e-3) on the whole matrix
+    y = portlib.apply(raw, ref["X"], capi.OP_N)
+    yt = portlib.apply(raw, ref["XT"], capi.OP_T)
+    assert np.linalg.norm(y - ref["Y"]) <= 1e-13 * np.linalg.norm(ref["Y"])
+    assert np.linalg.norm(yt - ref["YT"]) <= 1e-13 * np.linalg.norm(ref["YT"])
