@@ -107,6 +107,13 @@ BfCudaStatus uploadDirection(BfCudaPlan *P, DevDirection &dd) {
     cleanup();
     if (ce != cudaSuccess) return fail(BF_CUDA_ERROR_RUNTIME, std::string("value pool upload: ") + cudaGetErrorString(ce));
   }
+  if (!D.ownedValues.empty()) { // the copies behind merged leaves (bf_plan.cpp step 0) have been packed: drop them
+    for (DirOp &d : D.ops)
+      for (const std::vector<double> &v : D.ownedValues)
+        if (d.val == v.data()) { d.val = nullptr; break; }
+    D.ownedValues.clear();
+    D.ownedValues.shrink_to_fit();
+  }
   // (a value-less plan keeps the zeros of the memset above: it is ordered on P->stream, like the synthetic fill that
   // follows.  A second cudaMemset here ran on the LEGACY stream, which a non-blocking stream does not wait for, and
   // could zero tiles the fill had already written.)

@@ -2,6 +2,7 @@
 #include "bf_plan.hpp"
 
 #include <algorithm>
+#include <array>
 #include <climits>
 #include <complex>
 #include <cstdlib>
@@ -237,6 +238,88 @@ static void buildFused(const BfCudaPlanDesc &desc, Direction &D, const std::vect
   F.enabled = true;
 }
 
+// ---- step 0: stacks of small leaves -> one leaf ---------------------------------------------------------------
+// The reference's streamed factorizations end in a block column of ~1000 leaves of 5-12 rows each over a shared
+// column range (bfFacStreamer's Psi, src/fac.c:53-75; 2 120 leaves over 9 column ranges at 8 000 x 2 116).  Forward,
+// each is a ragged item of its own; transposed, every one of them contributes a tile of 8 rows x ~7 columns to the
+// same result rows: 352 000 tiles of 481 bytes, 0.08 of the HBM peak.  Leaves that are dense, not stored transposed,
+// hold host values, share (inBuf, inOff, k, outBuf, flags) and follow one another in the output rows are therefore
+// concatenated into one leaf (a copy of their values, owned by the Direction until the pool has been packed); the
+// same for leaves side by side in the operand rows, and for runs of identity leaves.  Value-less descriptors
+// (recordings, synthetic fills: values are defined per original leaf) and sharded ones are left alone.
+static bool mergeStackedEnabled() { const char *e = std::getenv("BF_PLAN_MERGE"); return !e || std::atoi(e) != 0; }
+
+static void mergeStackedLeaves(const BfCudaPlanDesc &desc, std::vector<BfCudaRawOp> &ops, std::vector<int64_t> &orig,
+                               std::vector<std::vector<double>> &owned) {
+  const size_t ed = desc.dtype == BF_CUDA_COMPLEX_F64 ? 2 : 1; // doubles per element
+  constexpr int64_t kSmall = 64; // mean extent along the stacking axis below which a run is worth merging
+  const int64_t n = (int64_t)ops.size();
+  std::vector<uint8_t> dead((size_t)n, 0);
+  auto mergeable = [&](const BfCudaRawOp &o) {
+    if (o.m <= 0 || o.k <= 0 || o.flags != 0u) return false; // any flag (TRANS / CONJ / REMOTE / owner): leave alone
+    if (o.kind == BF_CUDA_LEAF_IDENTITY) return o.m == o.k;
+    return o.kind == BF_CUDA_LEAF_DENSE && o.val != nullptr && o.ld >= o.k;
+  };
+  // pass 0: vertical stacks (dense), pass 1: horizontal stacks (dense), pass 2: identity runs
+  for (int pass = 0; pass < 3; ++pass) {
+    std::vector<int64_t> idx;
+    for (int64_t i = 0; i < n; ++i)
+      if (!dead[(size_t)i] && mergeable(ops[(size_t)i]) && (ops[(size_t)i].kind == BF_CUDA_LEAF_IDENTITY) == (pass == 2)) idx.push_back(i);
+    auto key = [&](int64_t i) {
+      const BfCudaRawOp &o = ops[(size_t)i];
+      if (pass == 0) return std::array<int64_t, 6>{o.inBuf, o.outBuf, o.inOff, o.k, o.outOff, i};
+      if (pass == 1) return std::array<int64_t, 6>{o.inBuf, o.outBuf, o.outOff, o.m, o.inOff, i};
+      return std::array<int64_t, 6>{o.inBuf, o.outBuf, o.outOff - o.inOff, 0, o.outOff, i};
+    };
+    std::sort(idx.begin(), idx.end(), [&](int64_t a, int64_t b) { return key(a) < key(b); });
+    for (size_t a = 0; a < idx.size();) {
+      size_t b = a + 1;
+      auto follows = [&](int64_t p, int64_t q) { // q continues p
+        const BfCudaRawOp &x = ops[(size_t)p], &y = ops[(size_t)q];
+        if (x.inBuf != y.inBuf || x.outBuf != y.outBuf) return false;
+        if (pass == 0) return x.inOff == y.inOff && x.k == y.k && x.outOff + x.m == y.outOff;
+        if (pass == 1) return x.outOff == y.outOff && x.m == y.m && x.inOff + x.k == y.inOff;
+        return x.outOff + x.m == y.outOff && x.inOff + x.k == y.inOff;
+      };
+      while (b < idx.size() && follows(idx[b - 1], idx[b])) ++b;
+      const size_t cnt = b - a;
+      int64_t ext = 0;
+      for (size_t j = a; j < b; ++j) ext += pass == 1 ? ops[(size_t)idx[j]].k : ops[(size_t)idx[j]].m;
+      if (cnt >= 2 && (pass == 2 || ext < kSmall * (int64_t)cnt)) {
+        const int64_t first = *std::min_element(idx.begin() + (std::ptrdiff_t)a, idx.begin() + (std::ptrdiff_t)b);
+        BfCudaRawOp M = ops[(size_t)idx[a]]; // lowest offset of the run
+        if (pass == 2) {
+          M.m = M.k = ext;
+        } else {
+          const int64_t rows = pass == 0 ? ext : M.m, cols = pass == 0 ? M.k : ext;
+          std::vector<double> buf;
+          try { buf.resize((size_t)rows * (size_t)cols * ed); } catch (const std::bad_alloc &) { a = b; continue; }
+          int64_t r0 = 0, c0 = 0;
+          for (size_t j = a; j < b; ++j) {
+            const BfCudaRawOp &o = ops[(size_t)idx[j]];
+            const double *src = static_cast<const double *>(o.val);
+            for (int64_t r = 0; r < o.m; ++r)
+              std::memcpy(buf.data() + ((size_t)(r0 + r) * (size_t)cols + (size_t)c0) * ed, src + (size_t)r * (size_t)o.ld * ed, (size_t)o.k * ed * sizeof(double));
+            if (pass == 0) r0 += o.m; else c0 += o.k;
+          }
+          M.m = rows; M.k = cols; M.ld = cols;
+          owned.push_back(std::move(buf));
+          M.val = owned.back().data();
+        }
+        for (size_t j = a; j < b; ++j) dead[(size_t)idx[j]] = 1;
+        dead[(size_t)first] = 0;
+        ops[(size_t)first] = M; // (orig[first] stays: the run is known by its first leaf)
+      }
+      a = b;
+    }
+  }
+  size_t w = 0;
+  for (int64_t i = 0; i < n; ++i)
+    if (!dead[(size_t)i]) { ops[w] = ops[(size_t)i]; orig[w] = orig[(size_t)i]; ++w; }
+  ops.resize(w);
+  orig.resize(w);
+}
+
 BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQueues, Direction &D,
                               std::string &err) {
   const bool cplx = desc.dtype == BF_CUDA_COMPLEX_F64;
@@ -263,13 +346,26 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
   D.outBufId = rev ? BF_CUDA_BUF_X : BF_CUDA_BUF_Y;
   D.rowsIn = desc.bufRows[D.inBufId];
   D.rowsOut = desc.bufRows[D.outBufId];
-  const int64_t nB = desc.numBufs, nOps = desc.numOps;
+  const int64_t nB = desc.numBufs;
+  // ---- 0. stacks of small leaves become one leaf (see mergeStackedLeaves) ----------------------
+  std::vector<BfCudaRawOp> rawOps(desc.ops, desc.ops + desc.numOps);
+  std::vector<int64_t> rawOrig((size_t)desc.numOps);
+  std::iota(rawOrig.begin(), rawOrig.end(), int64_t(0));
+  if (!sharded && mergeStackedEnabled()) {
+    bool sane = true; // (ranges are validated below, on whatever list we end up with; merge only what is sane)
+    for (const BfCudaRawOp &o : rawOps)
+      if (o.inBuf < 0 || o.inBuf >= nB || o.outBuf < 0 || o.outBuf >= nB || o.m < 0 || o.k < 0 || o.inOff < 0 || o.outOff < 0 ||
+          o.inOff + o.k > desc.bufRows[o.inBuf] || o.outOff + o.m > desc.bufRows[o.outBuf]) { sane = false; break; }
+    if (sane) mergeStackedLeaves(desc, rawOps, rawOrig, D.ownedValues);
+  }
+  const int64_t nOps = (int64_t)rawOps.size();
 
   // ---- 1. leaves as they act in this direction, in processing order -------------------------
   D.ops.reserve((size_t)nOps);
   for (int64_t n = 0; n < nOps; ++n) {
-    const int64_t ri = rev ? nOps - 1 - n : n;
-    const BfCudaRawOp &o = desc.ops[ri];
+    const int64_t rn = rev ? nOps - 1 - n : n;
+    const int64_t ri = rawOrig[(size_t)rn]; // index in the caller's list (of the first leaf of a merged run)
+    const BfCudaRawOp &o = rawOps[(size_t)rn];
     if (o.inBuf < 0 || o.inBuf >= nB || o.outBuf < 0 || o.outBuf >= nB || o.m < 0 || o.k < 0 ||
         o.inOff < 0 || o.outOff < 0 || o.inOff + o.k > desc.bufRows[o.inBuf] ||
         o.outOff + o.m > desc.bufRows[o.outBuf] || o.inBuf == o.outBuf) {

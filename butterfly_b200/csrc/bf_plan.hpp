@@ -150,6 +150,7 @@ struct Direction {
   int64_t entries = 0;
   int64_t numItems = 0, numTiles = 0, maxTileK = 0, maxItemRows = 0;
   FusedTables fused;
+  std::vector<std::vector<double>> ownedValues; // values of merged leaves (bf_plan.cpp step 0); dropped once the pool is packed
   int shardWorld = 0, shardRank = 0;  // > 1: one rank's share; the workspace is then flat (no row is reused inside
                                       // an apply: peers push into it at their own pace)
 };

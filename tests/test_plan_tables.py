@@ -146,3 +146,64 @@ def test_long_result_rows_are_spread_over_later_stages(op, monkeypatch):
     finally:
         t0.close()
         t1.close()
+
+
+def _stacked_leaves_operator(dtype, seed=41):
+    """The end of a streamed factorization (bfFacStreamer's Psi): a block column of many leaves of a few rows each
+    over shared column ranges, followed by a run of identity leaves; plus leaves side by side in the operand rows,
+    one stored transposed and one with a padded row stride (neither of which may be merged blindly)."""
+    from butterfly_b200.synth import _Builder
+
+    rng = np.random.default_rng(seed)
+    b = _Builder(dtype, True, rng)
+    n_in, mid, n_out = 300, 260, 411
+    t = b.new_buf(mid)      # X -> t: leaves side by side (k = 5..20 each) over three row blocks
+    u = b.new_buf(n_out)    # t -> u: vertical stacks over two column ranges
+    r0 = 0
+    for rows in (90, 100, 70):
+        c0 = 0
+        while c0 < n_in:
+            k = int(min(n_in - c0, rng.integers(5, 21)))
+            b.dense(0, c0, t, r0, rows, k, trans=(c0 == 0 and rows == 100), pad=(3 if c0 > 200 else 0))
+            c0 += k
+        r0 += rows
+    r = 0
+    while r < n_out:
+        m = int(min(n_out - r, rng.integers(3, 13)))
+        b.dense(t, 0, u, r, m, 200)
+        b.dense(t, 200, u, r, m, 60, pad=(2 if r % 2 else 0))
+        r += m
+    r = 0
+    while r < n_out:  # u -> Y: a run of identity leaves with the same cuts
+        m = int(min(n_out - r, rng.integers(3, 13)))
+        b.identity(u, r, 1, r, m, m)
+        r += m
+    return b.finish(n_out, n_in)
+
+
+@pytest.mark.parametrize("dtype", [capi.COMPLEX_F64, capi.REAL_F64])
+@pytest.mark.parametrize("op", [capi.OP_N, capi.OP_T])
+def test_stacks_of_small_leaves_are_merged(dtype, op, monkeypatch):
+    raw = _stacked_leaves_operator(dtype)
+    cplx = dtype == capi.COMPLEX_F64
+    x = _x(np.random.default_rng(6), raw.num_cols if op == capi.OP_N else raw.num_rows, 3, cplx)
+    y_ref = portlib.apply(raw, x, op)
+    counts = {}
+    for merge in ("0", "1"):
+        monkeypatch.setenv("BF_PLAN_MERGE", merge)
+        t = Tables(raw, op, num_queues=29)
+        try:
+            t.check_queues()
+            y = t.apply(x)
+            assert not np.isnan(y).any()
+            assert np.linalg.norm(y - y_ref) <= 1e-13 * np.linalg.norm(y_ref), merge
+            kc = t.tiles["kc"].astype(np.int64)
+            counts[merge] = (int((kc < 0xFFFD).sum()), len(t.items), sum(_stage_entries(t)))
+            if merge == "1" and t.fused:
+                yf, _ = t.apply_fused(x, "reverse", 0)
+                assert np.array_equal(yf, y)
+        finally:
+            t.close()
+    assert counts["1"][2] == counts["0"][2], "merging moves no entry in or out of the operator"
+    assert counts["1"][0] < 0.6 * counts["0"][0], counts  # far fewer (and wider / taller) tiles
+    assert counts["1"][1] < counts["0"][1], counts        # and fewer items
