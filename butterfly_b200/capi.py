@@ -25,6 +25,7 @@ OK = 0
 REAL_F64, COMPLEX_F64 = 0, 1
 OP_N, OP_T, OP_H = 0, 1, 2
 LEAF_DENSE, LEAF_IDENTITY, LEAF_DIAG = 0, 1, 2
+BUILD_KEEP_LEAVES = 4  # BF_CUDA_BUILD_KEEP_LEAVES: PlanDesc.buildTranspose bit 2
 LEAF_TRANS, LEAF_CONJ, LEAF_REMOTE = 2, 4, 8
 BUF_X, BUF_Y, BUF_FIRST_TEMP = 0, 1, 2
 

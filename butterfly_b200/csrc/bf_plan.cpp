@@ -320,6 +320,52 @@ static void mergeStackedLeaves(const BfCudaPlanDesc &desc, std::vector<BfCudaRaw
   orig.resize(w);
 }
 
+// An identity leaf that is the ONLY writer of a whole temporary B (B = A[off : off + m]) is a copy: whoever reads B
+// reads A instead.  One that is the only READER of a whole temporary A is a copy too: whoever writes A writes its
+// rows of the identity's output instead (other writers of those rows simply accumulate, as they did).  The streamed
+// factorizations of the reference carry such a factor at their row end (after step 0 it is ONE identity leaf over
+// all rows): a stage and a launch in each direction for nothing but a copy of the result / operand.
+static bool elideIdentityEnabled() { const char *e = std::getenv("BF_PLAN_ELIDE"); return !e || std::atoi(e) != 0; }
+
+static void elideIdentityCopies(const BfCudaPlanDesc &desc, std::vector<BfCudaRawOp> &ops, std::vector<int64_t> &orig) {
+  const int64_t nB = desc.numBufs;
+  for (bool again = true; again;) {
+    again = false;
+    std::vector<int64_t> writers((size_t)nB, 0), readers((size_t)nB, 0);
+    for (const BfCudaRawOp &o : ops)
+      if (o.m > 0 && o.k > 0) { ++writers[(size_t)o.outBuf]; ++readers[(size_t)o.inBuf]; }
+    for (size_t i = 0; i < ops.size(); ++i) {
+      const BfCudaRawOp I = ops[i];
+      if (I.kind != BF_CUDA_LEAF_IDENTITY || I.flags != 0u || I.m != I.k || I.m <= 0 || I.inBuf == I.outBuf) continue;
+      const int64_t A = I.inBuf, B = I.outBuf;
+      const bool tempA = A != BF_CUDA_BUF_X && A != BF_CUDA_BUF_Y, tempB = B != BF_CUDA_BUF_X && B != BF_CUDA_BUF_Y;
+      bool done = false;
+      if (tempB && writers[(size_t)B] == 1 && I.outOff == 0 && I.m == desc.bufRows[B]) {
+        bool ok = true; // (a reader of B must not end up reading the buffer it writes)
+        for (const BfCudaRawOp &o : ops) if (o.inBuf == B && o.outBuf == A) ok = false;
+        if (ok) {
+          for (BfCudaRawOp &o : ops) if (o.inBuf == B) { o.inBuf = A; o.inOff += I.inOff; }
+          done = true;
+        }
+      }
+      if (!done && tempA && readers[(size_t)A] == 1 && I.inOff == 0 && I.m == desc.bufRows[A]) {
+        bool ok = true;
+        for (const BfCudaRawOp &o : ops) if (o.outBuf == A && o.inBuf == B) ok = false;
+        if (ok) {
+          for (BfCudaRawOp &o : ops) if (o.outBuf == A) { o.outBuf = B; o.outOff += I.outOff; }
+          done = true;
+        }
+      }
+      if (done) {
+        ops.erase(ops.begin() + (std::ptrdiff_t)i);
+        orig.erase(orig.begin() + (std::ptrdiff_t)i);
+        again = true;
+        break;
+      }
+    }
+  }
+}
+
 BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQueues, Direction &D,
                               std::string &err) {
   const bool cplx = desc.dtype == BF_CUDA_COMPLEX_F64;
@@ -351,12 +397,14 @@ BfCudaStatus compileDirection(const BfCudaPlanDesc &desc, int32_t op, int numQue
   std::vector<BfCudaRawOp> rawOps(desc.ops, desc.ops + desc.numOps);
   std::vector<int64_t> rawOrig((size_t)desc.numOps);
   std::iota(rawOrig.begin(), rawOrig.end(), int64_t(0));
-  if (!sharded && mergeStackedEnabled()) {
+  if (!sharded && !(desc.buildTranspose & BF_CUDA_BUILD_KEEP_LEAVES) && mergeStackedEnabled()) {
     bool sane = true; // (ranges are validated below, on whatever list we end up with; merge only what is sane)
     for (const BfCudaRawOp &o : rawOps)
-      if (o.inBuf < 0 || o.inBuf >= nB || o.outBuf < 0 || o.outBuf >= nB || o.m < 0 || o.k < 0 || o.inOff < 0 || o.outOff < 0 ||
+      if ((o.flags & ~(BF_CUDA_LEAF_TRANS | BF_CUDA_LEAF_CONJ)) != 0u || // REMOTE / owner bits: somebody shards by leaf and buffer
+          o.inBuf < 0 || o.inBuf >= nB || o.outBuf < 0 || o.outBuf >= nB || o.m < 0 || o.k < 0 || o.inOff < 0 || o.outOff < 0 ||
           o.inOff + o.k > desc.bufRows[o.inBuf] || o.outOff + o.m > desc.bufRows[o.outBuf]) { sane = false; break; }
     if (sane) mergeStackedLeaves(desc, rawOps, rawOrig, D.ownedValues);
+    if (sane && elideIdentityEnabled()) elideIdentityCopies(desc, rawOps, rawOrig);
   }
   const int64_t nOps = (int64_t)rawOps.size();
 

@@ -63,7 +63,7 @@ class RawOps:
         d.numOps = len(ops)
         d.ops = ops.ctypes.data_as(C.POINTER(capi.RawOp))
         d.device = device
-        d.buildTranspose = int(build_transpose)
+        d.buildTranspose = int(build_transpose) | (capi.BUILD_KEEP_LEAVES if getattr(self, "keep_leaves", False) else 0)
         if shard is not None:  # (world, rank): one rank's share of a block-row sharded operator
             d.shardWorld, d.shardRank = int(shard[0]), int(shard[1])
         self._keep = ops  # the pointer table handed to C

@@ -240,6 +240,7 @@ def mask_for_rank(raw: RawOps, owner: np.ndarray, rank: int) -> RawOps:
         ops["val"][remote & (ops["kind"] == capi.LEAF_IDENTITY)] = 0
     out = RawOps(raw.dtype, raw.num_rows, raw.num_cols, raw.buf_rows, ops, raw.values)
     out.origin = getattr(raw, "origin", None)
+    out.keep_leaves = True  # every rank must compile the SAME stages and buffers, also the one that owns every leaf
     return out
 
 

@@ -113,6 +113,8 @@ typedef struct BfCudaRawOp {
                       left for bfCudaPlanFillSynthetic (benchmarks on synthetic factors) */
 } BfCudaRawOp;
 
+#define BF_CUDA_BUILD_KEEP_LEAVES 4
+
 typedef struct BfCudaPlanDesc {
   int32_t abiVersion;     /* BF_CUDA_ABI_VERSION */
   int32_t dtype;          /* BfCudaDtype of every dense leaf and of X, Y */
@@ -125,7 +127,10 @@ typedef struct BfCudaPlanDesc {
                              summation order used for every output row (deterministic) */
   int32_t device;         /* CUDA device ordinal, -1 = current device */
   int32_t buildTranspose; /* bit 0: also compile A^T (OP_T); bit 1: also compile A^H (OP_H,
-                             complex only).  Each extra direction holds its own packed pool. */
+                             complex only).  Each extra direction holds its own packed pool.
+                             bit 2 (BF_CUDA_BUILD_KEEP_LEAVES): compile the leaf list exactly as given — no
+                             merging of stacked small leaves, no elision of identity copies — for callers
+                             that reason about the plan's stages and buffers leaf by leaf */
   int32_t shardWorld;     /* 0 / 1: the whole operator on one device.  > 1: one rank's share of a block-row
                              sharded operator (bfCudaShardDesc builds these): leaves of other ranks carry
                              BF_CUDA_LEAF_REMOTE, every leaf its owner (BF_CUDA_LEAF_OWNER); forward only */

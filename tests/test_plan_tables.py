@@ -204,6 +204,19 @@ def test_stacks_of_small_leaves_are_merged(dtype, op, monkeypatch):
                 assert np.array_equal(yf, y)
         finally:
             t.close()
+    # the run of identity leaves u -> Y is ONE copy of a whole temporary once merged: elided, its writers store into Y
+    monkeypatch.setenv("BF_PLAN_MERGE", "1")
+    stages = {}
+    for elide in ("0", "1"):
+        monkeypatch.setenv("BF_PLAN_ELIDE", elide)
+        t = Tables(raw, op, num_queues=29)
+        try:
+            stages[elide] = t.num_stages
+            y = t.apply(x)
+            assert np.linalg.norm(y - y_ref) <= 1e-13 * np.linalg.norm(y_ref), elide
+        finally:
+            t.close()
+    assert stages["1"] == stages["0"] - 1, stages
     assert counts["1"][2] == counts["0"][2], "merging moves no entry in or out of the operator"
     assert counts["1"][0] < 0.6 * counts["0"][0], counts  # far fewer (and wider / taller) tiles
     assert counts["1"][1] < counts["0"][1], counts        # and fewer items
