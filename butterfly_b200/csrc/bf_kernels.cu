@@ -637,29 +637,69 @@ __global__ void __launch_bounds__(kWideThreads) bfWideStage(const __grid_constan
       const uint32_t slot = cSeq % kWideSlots;
       const T *A = reinterpret_cast<const T *>(smem + slot * kTileBytes);
 
-      // the operand row of step j + 1 is fetched while step j computes
-      T xa[CT];
+      // The operand rows of the NEXT U steps are fetched while these U compute; the sums run over j in order.
+      // ncu (profiles/r2zz_realwide_summary.txt): the loop was ISSUE-bound, not latency-bound — fp64 pipe active 20 %,
+      // issue slots 62 %, i.e. five other instructions per DFMA (per-load guards, 64-bit index multiplies, a
+      // row-count branch per row and step).  Hence: whole blocks of U steps run unguarded on precomputed pointers,
+      // only the last block of a tile and items of fewer than R rows take the guarded path.
+      constexpr int U = CT <= 2 ? 8 : 4;
+      const T *xq[CT]; // next operand row to fetch, per column of this thread
 #pragma unroll
-      for (int c = 0; c < CT; ++c) xa[c] = colOk[c] ? xp[32 * c] : S::zero();
+      for (int c = 0; c < CT; ++c) xq[c] = xp + 32 * c;
+      T xa[U][CT];
+      auto fetch = [&](T (&dst)[U][CT], int jb) { // rows jb .. jb + U - 1 of the tile's operand segment
+        if (jb + U <= kc) {
+#pragma unroll
+          for (int s = 0; s < U; ++s)
+#pragma unroll
+            for (int c = 0; c < CT; ++c) dst[s][c] = colOk[c] ? xq[c][(long long)s * ldIn] : S::zero();
+        } else {
+#pragma unroll
+          for (int s = 0; s < U; ++s)
+#pragma unroll
+            for (int c = 0; c < CT; ++c) dst[s][c] = (colOk[c] && jb + s < kc) ? xq[c][(long long)s * ldIn] : S::zero();
+        }
+#pragma unroll
+        for (int c = 0; c < CT; ++c) xq[c] += (long long)U * ldIn;
+      };
+      fetch(xa, 0);
       mbarWait(smemU32(&bars[slot]), (cSeq / kWideSlots) & 1u);
-      int ro[RT]; // row offsets into the tile; rows past the edge are clamped (never stored)
+      const T *Ap[RT]; // this thread's rows of the tile; rows past the edge are clamped (never stored)
 #pragma unroll
-      for (int u = 0; u < RT; ++u) ro[u] = min(u * TY + ty, rows - 1) * kc;
-#pragma unroll 2
-      for (int j = 0; j < kc; ++j) {
-        T xn[CT];
+      for (int u = 0; u < RT; ++u) Ap[u] = A + min(u * TY + ty, rows - 1) * kc;
+      const bool fullRows = (RT - 1) * TY < rows; // every row group of the thread tile exists (warp-uniform)
+#pragma unroll 1
+      for (int j0 = 0; j0 < kc; j0 += U) {
+        T xn[U][CT];
+        fetch(xn, j0 + U);
+        if (fullRows && j0 + U <= kc) {
 #pragma unroll
-        for (int c = 0; c < CT; ++c) xn[c] = (colOk[c] && j + 1 < kc) ? xp[(long long)(j + 1) * ldIn + 32 * c] : S::zero();
+          for (int s = 0; s < U; ++s)
 #pragma unroll
-        for (int u = 0; u < RT; ++u) {
-          if (u * TY < rows) { // warp-uniform
-            const T av = A[ro[u] + j];
+            for (int u = 0; u < RT; ++u) {
+              const T av = Ap[u][j0 + s];
 #pragma unroll
-            for (int c = 0; c < CT; ++c) S::fma(acc[u][c], av, xa[c]);
+              for (int c = 0; c < CT; ++c) S::fma(acc[u][c], av, xa[s][c]);
+            }
+        } else {
+#pragma unroll
+          for (int s = 0; s < U; ++s) {
+            if (j0 + s < kc) { // warp-uniform
+#pragma unroll
+              for (int u = 0; u < RT; ++u) {
+                if (u * TY < rows) { // warp-uniform
+                  const T av = Ap[u][j0 + s];
+#pragma unroll
+                  for (int c = 0; c < CT; ++c) S::fma(acc[u][c], av, xa[s][c]);
+                }
+              }
+            }
           }
         }
 #pragma unroll
-        for (int c = 0; c < CT; ++c) xa[c] = xn[c];
+        for (int s = 0; s < U; ++s)
+#pragma unroll
+          for (int c = 0; c < CT; ++c) xa[s][c] = xn[s][c];
       }
       __syncthreads(); // every warp is done with this slot
       produce();
